@@ -1,0 +1,56 @@
+"""The oracle pinned against every known-answer test the reference ships for this path
+(reference test/cpp/AlignmentTest.cpp, test/cpp/AlnGraphBoostTest.cpp, src/tests/test_aligngraph.py)."""
+import pytest
+
+from helpers import Oracle, Ref, have_ref, MODE_MERGE, MODE_SINGLE
+
+CHECKERS = ["orc"] + (["ref"] if have_ref() else [])
+
+
+def _mk(name):
+    return Oracle() if name == "orc" else Ref()
+
+
+@pytest.mark.parametrize("name", CHECKERS)
+def test_normalize_kats(name):
+    # AlignmentTest.cpp:19-47 (same three vectors as test_aligngraph.py:50-54)
+    c = _mk(name)
+    nt = (lambda q, t: c.normalize_trim(q, t, 1, 0)[:2]) if name == "orc" else (lambda q, t: c.normalize_trim(q, t, 1, 0, do_trim=False)[:2])
+    assert nt(b"CAC", b"CGC") == (b"C-AC", b"CG-C")
+    assert nt(b"-C--CGT", b"CCGAC-T") == (b"CCG--T", b"CCGACT")
+    q, t = nt(b"ATAT-AGCCGGC", b"ATATTA---GGC")
+    assert t == b"ATATTAG--G-C"
+    assert q == b"ATAT-AGCCGGC"
+
+
+@pytest.mark.parametrize("name", CHECKERS)
+def test_trim_kats(name):
+    # AlignmentTest.cpp:80-143
+    c = _mk(name)
+    t, q = b"ACG-TCA-GCA", b"AC-C-C-T---"
+    if name == "orc":
+        f = lambda k: c.trim(q, t, 1, k)
+    else:
+        pytest.skip("trimAln alone is only exposed after normalizeGaps in ref_capi; covered by fuzz")
+    assert f(0) == (q, t, 1)
+    assert f(3) == (b"C-C-T", b"-TCA-", 4)
+    assert f(4) == (b"C", b"C", 5)
+    qq, tt, st = f(5)
+    assert (qq, tt, st) == (b"", b"", 6)
+    qq, tt, _ = f(500)
+    assert (qq, tt) == (b"", b"")
+
+
+@pytest.mark.parametrize("name", CHECKERS)
+def test_raw_consensus_kat(name):
+    # AlnGraphBoostTest.cpp:11-47: un-normalised alignments, string ctor -> "ATATAGCCGGC"
+    c = _mk(name)
+    alns = [
+        (b"ATAT-AGCCGGC", b"ATATTA---GGC", 1),
+        (b"ATAT-ACGGC", b"ATATTA-GGC", 1),
+        (b"ATCAT--CCGGC", b"AT-ATTA--GGC", 1),
+        (b"ATAT-ACCGAG-", b"ATATTA--G-GC", 1),
+        (b"ATAT-AGCCGGC", b"ATATTA---GGC", 1),
+    ]
+    r = c.consensus(9, alns, backbone=b"ATATTAGGC", mode=MODE_MERGE | MODE_SINGLE, min_weight=0)
+    assert r["single"] == b"ATATAGCCGGC"
