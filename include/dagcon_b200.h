@@ -1,0 +1,151 @@
+/* dagcon_b200.h -- C ABI of libdagcon_b200.so: the DAGCon consensus hot path on B200 (sm_100a).
+ *
+ * The reference (verdurin/pbdagcon @ 3c382f2) has no FFI; its boundary for this path is the C++
+ * call pattern of the Consensus functor.  Each entry point below names the reference interface
+ * it replaces (file:line relative to the reference tree).  All functions return 0 on success
+ * or a negative DGC_E_* code; none throws, calls exit(), or falls back to a CPU path: when no
+ * CUDA device is usable dgc_create fails.
+ *
+ * Batch = what AlnProvider::nextTarget hands to the consumer (src/cpp/AlnProvider.hpp:39,43),
+ * for many targets at once: per target {tlen, [optional backbone string], its alignments in
+ * input order}; per alignment {1-based start, raw column count, qstr, tstr} exactly as the
+ * provider produced them (dagcon::Alignment, src/cpp/Alignment.hpp:12-42).  Normalisation,
+ * trimming, the min-length / min-coverage filters, graph construction, node merging, the
+ * best-path DP and fragment extraction all run on the device.
+ */
+#ifndef DAGCON_B200_H
+#define DAGCON_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGC_ABI_VERSION 1
+
+/* error codes (function return values) */
+#define DGC_OK 0
+#define DGC_E_INVALID (-1)   /* bad argument / malformed batch */
+#define DGC_E_CUDA (-2)      /* CUDA runtime error; see dgc_last_error */
+#define DGC_E_NOMEM (-3)     /* a single target does not fit the scratch budget */
+#define DGC_E_STATE (-4)     /* collect without submit, etc. */
+#define DGC_E_NODEVICE (-5)  /* no usable CUDA device (there is no CPU fallback) */
+
+/* per-target status (dgc_results.tgt_status) */
+#define DGC_T_OK 0
+#define DGC_T_SKIPPED 1       /* fewer than min_cov alignments: main.cpp:66-72,118; dazcon.cpp:69 */
+#define DGC_T_BAD_ALIGNMENT 2 /* an alignment runs off the backbone (reference: out-of-bounds
+                                 vertex access, AlnGraphBoost.cpp:73-79) or start < 1 */
+#define DGC_T_TOO_MANY_ALNS 3 /* more than 65000 alignments in one target (16-bit degrees) */
+#define DGC_T_INTERNAL 4      /* scratch overflow / inconsistent graph (cycle); never on valid input */
+
+/* dgc_opts.flags */
+#define DGC_F_NO_NORMALIZE 1u /* skip normalizeGaps (tests: AlnGraphBoostTest.cpp:11-47 feeds raw alignments) */
+#define DGC_F_NO_TRIM 2u      /* skip trimAln */
+#define DGC_F_NO_MERGE 4u     /* skip mergeNodes */
+#define DGC_F_SINGLE 8u       /* consensus(minWeight) -> one longest run (AlnGraphBoost.cpp:285-325)
+                                 instead of consensus(seqs,minWeight,minLen) (:327-373) */
+
+/* Replaces ProgramOpts (src/cpp/ProgramOpts.hpp:8-36) for this path. */
+typedef struct dgc_opts {
+    uint32_t min_cov;       /* -c: min alignments per target AND consensus minWeight (main.cpp:261) */
+    uint32_t min_len;       /* -m / dazcon -l: min raw alignment columns AND min fragment length */
+    uint32_t trim;          /* -t: target bases trimmed from both alignment ends */
+    uint32_t flags;         /* DGC_F_* */
+    int32_t device;         /* CUDA device ordinal */
+    uint32_t targets_per_warp; /* serial graph kernels: 0 = auto */
+    uint64_t scratch_bytes; /* HBM budget for the per-chunk graph arena; 0 = default (24 GiB) */
+} dgc_opts;
+
+/* Packed targets (SoA).  Host pointers; pinned memory (dgc_host_alloc) makes the H2D copy async.
+ * Offsets are byte offsets into `arena`.  Strings need not be aligned or NUL-terminated. */
+typedef struct dgc_batch {
+    uint32_t n_targets;
+    uint32_t n_alns;
+    const uint32_t* tgt_tlen;      /* [n_targets]   Alignment::tlen of alns[0] */
+    const uint32_t* tgt_aln_begin; /* [n_targets+1] CSR into the alignment arrays */
+    const uint64_t* tgt_bb_off;    /* [n_targets] backbone string (tlen bytes) for the
+                                      AlnGraphBoost(const std::string&) ctor (dazcon.cpp:76),
+                                      or NULL: AlnGraphBoost(size_t) (main.cpp:130) */
+    const uint32_t* aln_start;     /* [n_alns] Alignment::start, 1-based */
+    const uint32_t* aln_len;       /* [n_alns] qstr.length() == tstr.length() */
+    const uint64_t* aln_q_off;     /* [n_alns] */
+    const uint64_t* aln_t_off;     /* [n_alns] */
+    const uint8_t* arena;
+    uint64_t arena_bytes;
+} dgc_batch;
+
+/* Replaces std::vector<CnsResult> per target (src/cpp/AlnGraphBoost.hpp CnsResult; filled at
+ * AlnGraphBoost.cpp:327-373).  Memory is owned by the handle and stays valid until the next
+ * dgc_collect / dgc_run on it, or dgc_destroy. */
+typedef struct dgc_results {
+    uint32_t n_targets;
+    uint32_t n_frags;
+    const uint32_t* tgt_status;     /* [n_targets] DGC_T_* */
+    const uint32_t* tgt_frag_begin; /* [n_targets+1] */
+    const int32_t* frag_range0;     /* [n_frags] CnsResult::range[0] */
+    const int32_t* frag_range1;     /* [n_frags] CnsResult::range[1] */
+    const uint64_t* frag_seq_off;   /* [n_frags] into seq_arena */
+    const uint32_t* frag_seq_len;   /* [n_frags] */
+    const uint8_t* seq_arena;
+    uint64_t seq_bytes;
+} dgc_results;
+
+/* device time of the last run, per kernel (CUDA events on the launching stream) */
+typedef struct dgc_timings {
+    float ms_h2d, ms_normalize, ms_count, ms_build, ms_merge, ms_bestpath, ms_compact, ms_d2h, ms_total;
+    uint32_t launches;       /* kernels launched by the last run */
+    uint32_t chunks;
+    uint64_t arena_bytes;    /* graph arena bytes used (sum over chunks) */
+    uint64_t norm_cols;      /* normalised+trimmed columns fed to the graph */
+    uint64_t nodes, edges;   /* pre-merge graph size, summed over targets */
+} dgc_timings;
+
+typedef struct dgc_handle dgc_handle;
+typedef struct dgc_dbatch dgc_dbatch; /* a batch resident in HBM */
+
+int dgc_abi_version(void);
+int dgc_device_count(void);
+
+/* One handle per GPU and per submitting thread; replaces the N Consensus threads + the two
+ * BoundedBuffers (main.cpp:248-274, dazcon.cpp:211-230, BoundedBuffer.hpp:18-50). */
+int dgc_create(const dgc_opts* opts, dgc_handle** out);
+int dgc_destroy(dgc_handle* h);
+const char* dgc_last_error(dgc_handle* h); /* h may be NULL: error of the last failed dgc_create */
+
+/* Pinned host staging memory for dgc_batch arrays. */
+int dgc_host_alloc(void** p, uint64_t bytes);
+int dgc_host_free(void* p);
+
+/* Asynchronous pipeline: submit copies the batch H2D and enqueues the kernels on one of the
+ * handle's streams (the caller's buffers must stay untouched until the matching collect);
+ * collect returns results in submit order.  Replaces AlnBuf::push / CnsBuf::pop
+ * (main.cpp:87,120,144,168). */
+int dgc_submit(dgc_handle* h, const dgc_batch* batch);
+int dgc_collect(dgc_handle* h, dgc_results* out);
+
+/* Synchronous convenience: submit + collect. */
+int dgc_consensus(dgc_handle* h, const dgc_batch* batch, dgc_results* out);
+
+/* HBM-resident batches (benchmarking the kernels without the PCIe copy). */
+int dgc_upload(dgc_handle* h, const dgc_batch* batch, dgc_dbatch** out);
+int dgc_run(dgc_handle* h, dgc_dbatch* db, dgc_results* out);
+int dgc_dbatch_free(dgc_handle* h, dgc_dbatch* db);
+int dgc_get_timings(dgc_handle* h, dgc_timings* out);
+
+/* Test hooks (parity against the oracle at intermediate stages).
+ * dgc_debug_normalize: normalizeGaps+trimAln (Alignment.cpp:131-242) of every alignment of a
+ *   resident batch; out_cols receives (q | t<<8) per column at out_off[a] .. +out_len[a].
+ * dgc_debug_graph: text dump of one target's graph after build (stage 0) or after mergeNodes
+ *   (stage 1), one line per vertex: "id base weight coverage backbone deleted | dst:count:visited
+ *   ... | src:count:visited ..." (vertex ids = the reference's creation order). */
+int dgc_debug_normalize(dgc_handle* h, dgc_dbatch* db, uint16_t* out_cols, uint64_t out_cap,
+                        uint64_t* out_off, uint32_t* out_len, uint32_t* out_start, uint32_t* out_flags);
+int dgc_debug_graph(dgc_handle* h, dgc_dbatch* db, uint32_t target, int stage, char** text, uint64_t* n);
+void dgc_debug_free(char* text);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

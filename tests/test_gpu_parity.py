@@ -1,0 +1,270 @@
+"""GPU parity: libdagcon_b200.so (through its C ABI) against the oracle, stage by stage and end to end.
+Bit-exact is the bar: strings, vertex/edge lists in order, counts, flags, fragment ranges and sequences."""
+import random
+
+import numpy as np
+import pytest
+
+from helpers import (Oracle, Ref, have_ref, rand_target, MODE_PIPELINE, MODE_DUMP_PRE, MODE_DUMP_POST, MODE_NORM,
+                     MODE_TRIM, MODE_MERGE, MODE_SINGLE)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def api():
+    import pbdagcon_b200.api as api
+    return api
+
+
+@pytest.fixture(scope="module")
+def synth():
+    import pbdagcon_b200.synth as synth
+    return synth
+
+
+def _batch(api, synth, targets, with_backbone=False):
+    return api.PackedBatch.from_synth(synth.from_python(targets, with_backbone=with_backbone))
+
+
+def test_normalize_trim_kats(api, synth):
+    # reference test/cpp/AlignmentTest.cpp:19-47 and :80-143
+    eng = api.Consensus(min_cov=0, min_len=0, trim=0)
+    alns = [(b"CAC", b"CGC", 1), (b"-C--CGT", b"CCGAC-T", 1), (b"ATAT-AGCCGGC", b"ATATTA---GGC", 1)]
+    got = eng.debug_normalize(_batch(api, synth, [(20, None, alns)]))
+    assert got[0][:2] == (b"C-AC", b"CG-C")
+    assert got[1][:2] == (b"CCG--T", b"CCGACT")
+    assert got[2][:2] == (b"ATAT-AGCCGGC", b"ATATTAG--G-C")
+    eng.close()
+    t, q = b"ACG-TCA-GCA", b"AC-C-C-T---"
+    for k, exp in [(0, (q, t, 1)), (3, (b"C-C-T", b"-TCA-", 4)), (4, (b"C", b"C", 5)), (5, (b"", b"", 6))]:
+        eng = api.Consensus(min_cov=0, min_len=0, trim=k, flags=api.F_NO_NORMALIZE)
+        assert eng.debug_normalize(_batch(api, synth, [(20, None, [(q, t, 1)])]))[0] == exp
+        eng.close()
+    eng = api.Consensus(min_cov=0, min_len=0, trim=500, flags=api.F_NO_NORMALIZE)
+    assert eng.debug_normalize(_batch(api, synth, [(20, None, [(q, t, 1)])]))[0][:2] == (b"", b"")
+    eng.close()
+
+
+@pytest.mark.parametrize("trim", [0, 1, 2, 5, 10, 50, 500])
+def test_normalize_trim_fuzz(api, synth, trim):
+    o = Oracle()
+    rng = random.Random(1000 + trim)
+    alns = []
+    for it in range(4000):
+        n = rng.randint(1, 150) if it % 10 else rng.randint(150, 2500)
+        alpha = "ACGT-" if it % 3 else "ACGTN-."
+        if it % 7 == 0:
+            alpha = "AC-"          # long gap runs, many pulls
+        q = "".join(rng.choice(alpha) for _ in range(n)).encode()
+        t = "".join(rng.choice(alpha) for _ in range(n)).encode()
+        alns.append((q, t, rng.randint(1, 1000)))
+    eng = api.Consensus(min_cov=0, min_len=0, trim=trim)
+    got = eng.debug_normalize(_batch(api, synth, [(100000, None, alns)]))
+    eng.close()
+    for (q, t, s), g in zip(alns, got):
+        assert g == o.normalize_trim(q, t, s, trim), (q, t, trim)
+
+
+def test_normalize_min_len_filter(api, synth):
+    eng = api.Consensus(min_cov=0, min_len=10, trim=0)
+    got = eng.debug_normalize(_batch(api, synth, [(50, None, [(b"ACGT", b"ACGT", 1), (b"ACGTACGTACGT", b"ACGTACGTACGT", 1)])]))
+    eng.close()
+    assert got[0] is None and got[1] == (b"ACGTACGTACGT", b"ACGTACGTACGT", 1)
+
+
+def _fuzz_targets(seed, n, **kw):
+    rng = random.Random(seed)
+    out = []
+    for it in range(n):
+        full = it % 4 == 0
+        L, bb, alns = rand_target(rng, err=rng.choice([0.05, 0.15, 0.3]), full=full,
+                                  alphabet="ACGT" if it % 5 else "ACGTN", dots=(it % 7 == 0), **kw)
+        out.append((L, bb, alns))
+    return out
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_graph_dumps_fuzz(api, synth, seed):
+    """Every vertex, both adjacency lists in order, counts and visited flags, before and after mergeNodes."""
+    o = Oracle()
+    targets = _fuzz_targets(200 + seed, 40)
+    trim = [0, 3, 10, 0][seed]
+    use_bb = seed % 2 == 1
+    eng = api.Consensus(min_cov=0, min_len=0, trim=trim)
+    b = _batch(api, synth, targets, with_backbone=use_bb)
+    for ti, (L, bb, alns) in enumerate(targets):
+        exp = o.consensus(L, alns, backbone=bb if use_bb else None, mode=MODE_PIPELINE | MODE_DUMP_PRE | MODE_DUMP_POST, trim=trim)
+        lines = exp["dump"].split("\n")
+        nl = (len(lines) - 1) // 2
+        pre, post = "\n".join(lines[:nl]) + "\n", "\n".join(lines[nl:2 * nl]) + "\n"
+        assert eng.debug_graph(b, ti, 0) == pre, f"pre-merge graph differs target {ti}"
+        assert eng.debug_graph(b, ti, 1) == post, f"post-merge graph differs target {ti}"
+    eng.close()
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_consensus_fuzz(api, synth, seed):
+    o = Oracle()
+    r = Ref() if have_ref() else None
+    rng = random.Random(300 + seed)
+    targets = _fuzz_targets(300 + seed, 150)
+    trim = rng.choice([0, 3, 10])
+    minw = rng.choice([0, 1, 2, 4])
+    minlen = rng.choice([0, 5, 20])
+    use_bb = seed % 2 == 0
+    eng = api.Consensus(min_cov=minw, min_len=minlen, trim=trim)
+    res = eng(_batch(api, synth, targets, with_backbone=use_bb))
+    eng.close()
+    for ti, (L, bb, alns) in enumerate(targets):
+        if len(alns) < minw:
+            assert res.status[ti] == api.T_SKIPPED and res.frags(ti) == []
+            continue
+        exp = o.consensus(L, alns, backbone=bb if use_bb else None, mode=MODE_PIPELINE, trim=trim, min_weight=minw, min_len=minlen)
+        assert res.status[ti] == api.T_OK
+        assert res.frags(ti) == exp["frags"], f"target {ti}"
+        if r is not None and ti % 5 == 0:
+            assert res.frags(ti) == r.consensus(L, alns, backbone=bb if use_bb else None, mode=MODE_PIPELINE, trim=trim,
+                                                min_weight=minw, min_len=minlen)["frags"]
+
+
+def test_raw_consensus_kat(api, synth):
+    # reference test/cpp/AlnGraphBoostTest.cpp:11-47
+    alns = [
+        (b"ATAT-AGCCGGC", b"ATATTA---GGC", 1),
+        (b"ATAT-ACGGC", b"ATATTA-GGC", 1),
+        (b"ATCAT--CCGGC", b"AT-ATTA--GGC", 1),
+        (b"ATAT-ACCGAG-", b"ATATTA--G-GC", 1),
+        (b"ATAT-AGCCGGC", b"ATATTA---GGC", 1),
+    ]
+    eng = api.Consensus(min_cov=0, min_len=0, trim=0, flags=api.F_NO_NORMALIZE | api.F_NO_TRIM | api.F_SINGLE)
+    res = eng(_batch(api, synth, [(9, b"ATATTAGGC", alns)], with_backbone=True))
+    eng.close()
+    assert [f[2] for f in res.frags(0)] == [b"ATATAGCCGGC"]
+
+
+@pytest.mark.parametrize("flags_mode", [(1, MODE_TRIM | MODE_MERGE), (2, MODE_NORM | MODE_MERGE), (4, MODE_NORM | MODE_TRIM),
+                                        (8, MODE_PIPELINE | MODE_SINGLE)])
+def test_mode_flags(api, synth, flags_mode):
+    flags, mode = flags_mode
+    o = Oracle()
+    targets = _fuzz_targets(77, 60)
+    if flags & 1:   # feed already-normalised strings so that un-normalised addAln stays well defined
+        targets = [(L, bb, [o.normalize_trim(q, t, s, 0) for q, t, s in alns]) for L, bb, alns in targets]
+    eng = api.Consensus(min_cov=2, min_len=0, trim=3, flags=flags)
+    res = eng(_batch(api, synth, targets))
+    eng.close()
+    for ti, (L, bb, alns) in enumerate(targets):
+        if len(alns) < 2:
+            continue
+        exp = o.consensus(L, alns, mode=mode, trim=3, min_weight=2, min_len=0)
+        if flags & 8:
+            assert [f[2] for f in res.frags(ti)] == [exp["single"]], f"target {ti}"
+        else:
+            assert res.frags(ti) == exp["frags"], f"target {ti}"
+
+
+def test_edge_cases(api, synth):
+    o = Oracle()
+    eng = api.Consensus(min_cov=1, min_len=0, trim=0)
+    # empty batch
+    res = eng(api.PackedBatch(np.zeros(0, np.uint32), np.zeros(1, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.uint32),
+                              np.zeros(0, np.uint64), np.zeros(0, np.uint64), np.zeros(16, np.uint8)))
+    assert res.n_targets == 0
+    targets = [
+        (10, None, []),                                              # no alignments -> skipped
+        (10, None, [(b"ACGTACGTAC", b"ACGTACGTAC", 1)]),             # perfect full-length match
+        (10, None, [(b"ACGTACGTACG", b"ACGTACGTACG", 1)]),           # runs one base off the backbone -> rejected
+        (10, None, [(b"ACG", b"ACG", 0)]),                           # start 0 -> rejected
+        (10, None, [(b"----", b"ACGT", 3)]),                         # deletions only
+        (10, None, [(b"ACGT", b"----", 5)]),                         # insertions only
+        (10, None, [(b"AC", b"AC", 9), (b"AC", b"AC", 1)]),          # touches both backbone ends
+        (1, None, [(b"A", b"A", 1), (b"A", b"A", 1), (b"C", b"-", 1), (b"C", b"-", 2)]),
+        (5, None, [(b"-", b"-", 1), (b".", b".", 2)]),               # all-gap columns normalise to empty alignments
+    ]
+    res = eng(_batch(api, synth, targets))
+    eng.close()
+    assert res.status[0] == api.T_SKIPPED
+    assert res.status[2] == api.T_BAD_ALIGNMENT and res.frags(2) == []
+    assert res.status[3] == api.T_BAD_ALIGNMENT
+    for ti in (1, 4, 5, 6, 7, 8):
+        L, _, alns = targets[ti]
+        exp = o.consensus(L, alns, mode=MODE_PIPELINE, trim=0, min_weight=1, min_len=0)
+        assert exp["status"] == 0
+        assert res.status[ti] == api.T_OK
+        assert res.frags(ti) == exp["frags"], f"target {ti}"
+
+
+def test_min_len_and_min_cov_filters(api, synth):
+    """main.cpp:66-72,118 (targets with < minCov alignments) and :132 (raw columns < minLen are skipped but still
+    count toward minCov); fragments shorter than minLen are dropped (AlnGraphBoost.cpp:359,371)."""
+    o = Oracle()
+    targets = _fuzz_targets(55, 80, min_span=5)
+    eng = api.Consensus(min_cov=3, min_len=60, trim=2)
+    res = eng(_batch(api, synth, targets))
+    eng.close()
+    seen_skip = seen_frag = False
+    for ti, (L, bb, alns) in enumerate(targets):
+        if len(alns) < 3:
+            assert res.status[ti] == api.T_SKIPPED
+            seen_skip = True
+            continue
+        exp = o.consensus(L, alns, mode=MODE_PIPELINE, trim=2, min_weight=3, min_len=60)
+        assert res.frags(ti) == exp["frags"]
+        seen_frag |= bool(exp["frags"])
+    assert seen_skip and seen_frag
+
+
+@pytest.mark.parametrize("shape", [(2000, 10, 6), (8000, 30, 3), (20000, 50, 1)])
+def test_synthetic_config_shapes(api, synth, shape):
+    """PacBio-like synthetic targets of the BASELINE config shapes, pbdagcon flags -c 8 -m 500 -t 50."""
+    L, cov, nt = shape
+    o = Oracle()
+    sb = synth.gen_batch(seed=2, L=L, cov=cov, t0=0, nt=nt)
+    eng = api.Consensus(min_cov=8, min_len=500, trim=50)
+    res = eng(api.PackedBatch.from_synth(sb))
+    eng.close()
+    for ti in range(nt):
+        exp = o.consensus(L, sb.target_alns(ti), mode=MODE_PIPELINE, trim=50, min_weight=8, min_len=500)
+        assert res.status[ti] == api.T_OK
+        assert res.frags(ti) == exp["frags"], f"target {ti}"
+        assert sum(len(f[2]) for f in res.frags(ti)) > 0.4 * L
+
+
+def test_chunking_and_targets_per_warp_do_not_change_results(api, synth):
+    sb = synth.gen_batch(seed=9, L=1500, cov=12, t0=0, nt=96)
+    pb = api.PackedBatch.from_synth(sb)
+    base = None
+    for tpw, scratch in [(1, 0), (4, 0), (32, 0), (2, 3 << 20)]:
+        eng = api.Consensus(min_cov=4, min_len=100, trim=20, targets_per_warp=tpw, scratch_bytes=scratch)
+        res = eng(pb)
+        tm = eng.timings()
+        eng.close()
+        got = [res.frags(t) for t in range(res.n_targets)]
+        if scratch:
+            assert tm["chunks"] > 1
+        if base is None:
+            base = got
+            o = Oracle()
+            for t in (0, 50, 95):
+                assert got[t] == o.consensus(1500, sb.target_alns(t), mode=MODE_PIPELINE, trim=20, min_weight=4, min_len=100)["frags"]
+        assert got == base
+
+
+def test_async_submit_collect_order(api, synth):
+    """dgc_submit/dgc_collect: two batches in flight, results come back in submit order and equal the synchronous call."""
+    eng = api.Consensus(min_cov=4, min_len=100, trim=20)
+    pbs = [api.PackedBatch.from_synth(synth.gen_batch(seed=20 + i, L=1200, cov=10, t0=0, nt=8)) for i in range(5)]
+    sync = [[eng(pb).frags(t) for t in range(8)] for pb in pbs]
+    got = []
+    eng.submit(pbs[0])
+    for i in range(1, 5):
+        eng.submit(pbs[i])
+        r = eng.collect()
+        got.append([r.frags(t) for t in range(8)])
+    r = eng.collect()
+    got.append([r.frags(t) for t in range(8)])
+    with pytest.raises(api.DagconError):
+        eng.collect()
+    eng.close()
+    assert got == sync
