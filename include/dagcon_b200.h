@@ -95,6 +95,7 @@ typedef struct dgc_results {
 /* device time of the last run, per kernel (CUDA events on the launching stream) */
 typedef struct dgc_timings {
     float ms_h2d, ms_normalize, ms_count, ms_build, ms_merge, ms_bestpath, ms_compact, ms_d2h, ms_total;
+    float ms_span;           /* first event to last event on the stream: includes host planning gaps */
     uint32_t launches;       /* kernels launched by the last run */
     uint32_t chunks;
     uint64_t arena_bytes;    /* graph arena bytes used (sum over chunks) */

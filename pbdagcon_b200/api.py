@@ -47,7 +47,7 @@ class CResults(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("ms_h2d", "ms_normalize", "ms_count", "ms_build", "ms_merge", "ms_bestpath",
-                                         "ms_compact", "ms_d2h", "ms_total")] + \
+                                         "ms_compact", "ms_d2h", "ms_total", "ms_span")] + \
                [("launches", C.c_uint32), ("chunks", C.c_uint32), ("arena_bytes", C.c_uint64), ("norm_cols", C.c_uint64),
                 ("nodes", C.c_uint64), ("edges", C.c_uint64)]
 

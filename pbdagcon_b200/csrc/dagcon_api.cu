@@ -464,6 +464,8 @@ void finish_timings(Slot& s) {
     s.tm.ms_merge = acc[PH_MERGE]; s.tm.ms_bestpath = acc[PH_PATH]; s.tm.ms_compact = acc[PH_COMPACT]; s.tm.ms_d2h = acc[PH_D2H];
     s.tm.ms_total = 0;
     for (int i = 0; i < PH_N; i++) s.tm.ms_total += acc[i];
+    s.tm.ms_span = 0;
+    if (!s.spans.empty()) cudaEventElapsedTime(&s.tm.ms_span, s.spans.front().second.first, s.spans.back().second.second);
 }
 
 void begin_run(Slot& s) {
