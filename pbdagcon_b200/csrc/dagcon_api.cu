@@ -98,7 +98,7 @@ struct Slot {
     HostBuf hp_plan_in;   // status, V, E, cols read back after the plan kernel
     HostBuf hp_plan_out;  // the offset arrays
     // chunk arenas
-    DevBuf nodes, edges, cov, cons, frags, gscratch;
+    DevBuf nodes, edges, cov, cons, frags, gscratch, gacc;
     // compacted outputs
     DevBuf out_cons, out_frags;
     HostBuf r_status, r_cons_coff, r_frag_coff, r_totals, r_cons, r_frags, r_nfrag;
@@ -126,6 +126,7 @@ struct dgc_handle {
     dgc_opts opts{};
     int device = 0;
     int sm_count = 148;
+    size_t build_smem_max = 0;
     std::string err;
     Slot slots[NSLOT];
     uint64_t submitted = 0, collected = 0;
@@ -239,7 +240,7 @@ int launch_normalize(Slot& s, const dgc_dbatch& db) {
     return DGC_OK;
 }
 
-struct Chunk { uint32_t first, count; uint64_t nV, nE, nCov, nCons, nFrag, nGs; };
+struct Chunk { uint32_t first, count; uint64_t nV, nE, nCov, nCons, nFrag, nGs; uint32_t maxL2; };
 
 // The whole hot path for a resident batch.  stop_after: 0 build, 1 merge, 2 everything.
 int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) {
@@ -302,8 +303,8 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     uint32_t* p_gcap = p_fcap + (T + 1);
     uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (24ull << 30);
     std::vector<Chunk> chunks;
-    Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
-    auto chunk_bytes = [](const Chunk& c) { return 32 * c.nV + 32 * c.nE + 4 * c.nCov + c.nCons + 8 * c.nFrag + 4 * c.nGs; };
+    Chunk cur{0, 0, 0, 0, 0, 0, 0, 0, 0};
+    auto chunk_bytes = [](const Chunk& c) { return 32 * c.nV + 32 * c.nE + 12 * c.nCov + c.nCons + 8 * c.nFrag + 4 * c.nGs; };
     uint64_t out_cons_cap = 0, out_frag_cap = 0;
     for (size_t t = 0; t < T; t++) {
         const bool ok = hp_status[t] == T_OK && (only_target == 0xFFFFFFFFu || only_target == t);
@@ -312,17 +313,18 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         const uint32_t A = db.h_aln_begin[t + 1] - db.h_aln_begin[t];
         const uint64_t fcap = ok ? V / ((uint64_t)o.min_len + 1) + 2 : 0, gcap = ok ? 8ull * (A + 2) + 64 : 0;
         const uint64_t consb = (V + 15) & ~15ull;
-        Chunk one{0, 1, V, E, L2, consb, fcap, gcap};
+        Chunk one{0, 1, V, E, L2, consb, fcap, gcap, (uint32_t)L2};
         if (chunk_bytes(one) > budget) { s.err = "one target needs more than scratch_bytes of graph arena"; return DGC_E_NOMEM; }
         Chunk nxt = cur;
         nxt.nV += V; nxt.nE += E; nxt.nCov += L2; nxt.nCons += consb; nxt.nFrag += fcap; nxt.nGs += gcap; nxt.count++;
         if (cur.count && (chunk_bytes(nxt) > budget || cur.count >= (1u << 20))) {
             chunks.push_back(cur);
-            cur = Chunk{(uint32_t)t, 0, 0, 0, 0, 0, 0, 0};
+            cur = Chunk{(uint32_t)t, 0, 0, 0, 0, 0, 0, 0, 0};
         }
         p_node[t] = cur.nV; p_edge[t] = cur.nE; p_cov[t] = cur.nCov; p_cons[t] = cur.nCons; p_frag[t] = cur.nFrag; p_gs[t] = cur.nGs;
         p_fcap[t] = (uint32_t)fcap; p_gcap[t] = (uint32_t)gcap;
         cur.nV += V; cur.nE += E; cur.nCov += L2; cur.nCons += consb; cur.nFrag += fcap; cur.nGs += gcap; cur.count++;
+        cur.maxL2 = std::max(cur.maxL2, (uint32_t)L2);
         out_cons_cap += V; out_frag_cap += fcap;
         s.tm.nodes += V; s.tm.norm_cols += ok ? hp_cols[t] : 0;
     }
@@ -337,6 +339,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     s.tm.chunks = (uint32_t)chunks.size();
     CU(s.nodes.ensure(32 * mV + 64)); CU(s.edges.ensure(32 * mE + 64)); CU(s.cov.ensure(4 * mCov + 64));
     CU(s.cons.ensure(mCons + 64)); CU(s.frags.ensure(8 * mFrag + 64)); CU(s.gscratch.ensure(4 * mGs + 64));
+    CU(s.gacc.ensure(8 * mCov + 64));
     CU(s.out_cons.ensure(out_cons_cap + 64)); CU(s.out_frags.ensure(8 * out_frag_cap + 64));
     CU(cudaMemcpyAsync(s.node_off.p, p_node, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.edge_off.p, p_edge, 8 * T, cudaMemcpyHostToDevice, st));
@@ -358,8 +361,12 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         ba.cov_off = s.cov_off.as<u64>(); ba.norm = s.norm.as<u16>(); ba.a_off = s.o_off.as<u64>(); ba.a_len = s.o_len.as<u32>();
         ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>(); ba.nodes = s.nodes.as<Node>(); ba.edges = s.edges.as<Edge>();
         ba.cov = s.cov.as<int>(); ba.tgt_ne = s.t_ne.as<u32>(); ba.tgt_nv = s.t_nv.as<u32>();
+        // backbone accumulators: 8 B per position in shared memory when the longest backbone of the chunk fits
+        ba.smem_positions = std::min<uint32_t>(c.maxL2, (uint32_t)(h->build_smem_max / 8));
+        ba.gacc = s.gacc.as<u16>();
+        const size_t build_smem = 8ull * ba.smem_positions;
         span_begin(s, PH_BUILD);
-        k_build_graph<<<c.count, BT, 0, st>>>(ba);
+        k_build_graph<<<c.count, BT, build_smem, st>>>(ba);
         s.tm.launches++;
         CU(cudaGetLastError());
         span_end(s);
@@ -369,7 +376,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         sa.first = c.first; sa.count = c.count;
         uint32_t tpw = o.targets_per_warp;
         if (tpw == 0) { tpw = 1; while (tpw < 32 && c.count / tpw > (uint32_t)h->sm_count * 40u) tpw *= 2; }
-        if (tpw > 32) tpw = 32;
+        if (tpw > 4) tpw = 4;  // the fast path needs 256 words of shared memory per worker
         while (tpw & (tpw - 1)) tpw &= tpw - 1;
         sa.tpw = tpw; sa.flags = o.flags; sa.min_weight = o.min_cov; sa.min_len = o.min_len;
         sa.tgt_tlen = db.tgt_tlen.as<u32>(); sa.tgt_aln_begin = db.tgt_aln_begin.as<u32>(); sa.tgt_status = s.t_status.as<u32>();
@@ -540,6 +547,13 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
     h->opts = *opts;
     h->device = opts->device;
     h->sm_count = prop.multiProcessorCount;
+    {   // opt in to large dynamic shared memory for the build kernel (static use is ~4.2 KB)
+        size_t optin = prop.sharedMemPerBlockOptin > 8192 ? prop.sharedMemPerBlockOptin - 8192 : 0;
+        optin = std::min<size_t>(optin, 200 * 1024);
+        if (cudaFuncSetAttribute(k_build_graph, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)optin) == cudaSuccess)
+            h->build_smem_max = optin;
+        else { cudaGetLastError(); h->build_smem_max = 40 * 1024; }
+    }
     for (int i = 0; i < NSLOT; i++) {
         Slot& s = h->slots[i];
         s.h = h; s.index = i;
@@ -571,7 +585,7 @@ int dgc_destroy(dgc_handle* h) {
         for (DevBuf* b : {&s.o_off, &s.o_len, &s.o_start, &s.o_flags, &s.o_nI, &s.o_nE, &s.o_tkept, &s.norm, &s.t_status, &s.t_V,
                           &s.t_E, &s.t_cols, &s.t_ne, &s.t_nv, &s.t_cons_len, &s.t_nfrag, &s.t_cons_coff, &s.t_frag_coff, &s.totals,
                           &s.node_off, &s.edge_off, &s.cov_off, &s.cons_off, &s.frag_off, &s.frag_cap, &s.gs_off, &s.gs_cap,
-                          &s.nodes, &s.edges, &s.cov, &s.cons, &s.frags, &s.gscratch, &s.out_cons, &s.out_frags})
+                          &s.nodes, &s.edges, &s.cov, &s.cons, &s.frags, &s.gscratch, &s.gacc, &s.out_cons, &s.out_frags})
             b->release();
         for (HostBuf* b : {&s.h_norm_off, &s.hp_plan_in, &s.hp_plan_out, &s.r_status, &s.r_cons_coff, &s.r_frag_coff, &s.r_totals,
                            &s.r_cons, &s.r_frags, &s.r_nfrag})

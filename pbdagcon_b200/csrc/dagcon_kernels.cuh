@@ -9,7 +9,7 @@
 //   k_compact         CnsResult packing for the D2H copy
 //
 // Data layout in HBM (per target, offsets from k_target_plan's counts):
-//   Node[V]  32 B  {in_head, out_head, deg(in16|out16), weight, bbmap, base|flags|vis, score, best}
+//   Node[V]  32 B  {deg(in16|out16), base|flags|vis, in_head, out_head | weight, bbmap, score, best}
 //   Edge[E]  32 B  {src, dst, count, visited, next_out, prev_out, next_in, prev_in}
 //   cov[L+2] int   coverage of backbone vertices (only they are ever incremented, :76,87)
 // Vertex ids are the reference's: 0 enter, 1..L backbone, L+1 exit, then insertion vertices in
@@ -45,11 +45,11 @@ typedef unsigned long long u64;
 #define F_SINGLE 8u
 
 struct __align__(16) Node {
-    u32 in_head, out_head;
     u32 deg;  // in_deg | out_deg << 16
+    u32 bfv;  // base | flags << 8 | visited-in-edge count << 16
+    u32 in_head, out_head;
     int weight;
     u32 bbmap;  // _bbMap[v]; 0 for enter/exit (std::map default, AlnGraphBoost.cpp:407)
-    u32 bfv;    // base | flags << 8 | visited-in-edge count << 16
     union {
         float score;
         int cnt;
@@ -264,8 +264,14 @@ __global__ void k_target_plan(PlanArgs a) {
 // K2: graph construction, one 256-thread block per target.  Alignments are replayed in input
 // order (the adjacency-list order of every vertex is the order in which addEdge first created
 // each edge, AlnGraphBoost.cpp:109-127); inside one alignment every vertex is entered and left
-// at most once, so all of its columns are processed in parallel: block scans give each column
-// its backbone position, its insertion-vertex id and its predecessor on the path.
+// at most once, so all of its columns are processed in parallel (4 per thread, 1024 per tile):
+// block scans give each column its backbone position, its insertion-vertex id and its
+// predecessor on the path.
+// The per-backbone-position sums that every match/deletion column touches (coverage, weight,
+// count of the ctor edge p->p+1, last target base) live in shared memory as 16-bit counters
+// for the whole replay and are written to the vertex/edge records once at the end: without
+// that every alignment re-streams the target's backbone records through DRAM (ncu, round 1:
+// 38 GB of DRAM traffic per 1000 targets, 17x the arena size).
 struct BuildArgs {
     u32 first;  // first target of this chunk
     const u32* tgt_tlen;
@@ -286,9 +292,13 @@ struct BuildArgs {
     int* cov;
     u32* tgt_ne;  // edges in use after the build
     u32* tgt_nv;
+    u32 smem_positions;  // backbone positions (L+2) the dynamic shared memory can hold
+    u16* gacc;           // global fallback for longer backbones: 4 u16 per position, at 4*cov_off
 };
 
 #define BT 256
+#define CPT 4
+#define TILE (BT * CPT)
 __device__ __forceinline__ void block_scan2(u32 vs, u32 vm, u32& ex_s, u32& ex_m, u32& tot_s, u32& tot_m,
                                             u32* sa, u32* sb) {
     const u32 lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -346,8 +356,14 @@ __global__ void __launch_bounds__(BT) k_build_graph(BuildArgs a) {
     Edge* E = a.edges + a.edge_off[t];
     int* cov = a.cov + a.cov_off[t];
     const u32 ENTER = 0, EXIT = L + 1;
-    __shared__ u32 sa[BT / 32], sb[BT / 32], s_cur[BT];
+    __shared__ u32 sa[BT / 32], sb[BT / 32], s_cur[TILE];
     __shared__ u32 s_carry_t, s_carry_i, s_last, s_ecur, s_ins;
+    extern __shared__ __align__(16) u16 s_acc[];
+    // per-position accumulators: coverage, match weight, ctor-edge count, last target base
+    u16* accCov = (L + 2 <= a.smem_positions) ? s_acc : a.gacc + 4 * a.cov_off[t];
+    u16* accW = accCov + (L + 2);
+    u16* accC = accW + (L + 2);
+    u16* accB = accC + (L + 2);
 
     // ctor: AlnGraphBoost(size_t) :41-62 / AlnGraphBoost(const std::string&) :16-39
     const u8* bb = a.tgt_bb_off ? a.arena + a.tgt_bb_off[t] : nullptr;
@@ -364,7 +380,7 @@ __global__ void __launch_bounds__(BT) k_build_graph(BuildArgs a) {
         nd.cnt = 0;
         nd.best = NIL;
         N[p] = nd;
-        cov[p] = 0;
+        accCov[p] = 0; accW[p] = 0; accC[p] = 0; accB[p] = 0;
         if (p <= L) {
             Edge ed;
             ed.src = p; ed.dst = p + 1; ed.count = 0; ed.visited = 0;
@@ -382,58 +398,87 @@ __global__ void __launch_bounds__(BT) k_build_graph(BuildArgs a) {
         const u16* cols = a.norm + a.a_off[k];
         if (tid == 0) { s_carry_t = 0; s_carry_i = 0; s_last = ENTER; }
         __syncthreads();
-        for (u32 c0 = 0; c0 < n; c0 += BT) {
-            const u32 c = c0 + tid;
-            u32 q = 0, tch = 1;
-            bool valid = c < n;
-            if (valid) { u32 col = cols[c]; q = col & 0xFFu; tch = col >> 8; }
-            // column classes exactly as addAln tests them (:75, :84, :93)
-            const bool isM = valid && q == tch;
-            const bool isD = valid && !isM && q == DASH;
-            const bool isI = valid && !isM && !isD && tch == DASH;
-            const bool path = isM || isI;
-            u32 ex_s, ex_m, tot_s, tot_m;
-            block_scan2(((isM || isD) ? 1u : 0u) | (isI ? 0x10000u : 0u), path ? tid + 1 : 0u, ex_s, ex_m, tot_s,
-                        tot_m, sa, sb);
-            const u32 bbpos = start + s_carry_t + (ex_s & 0xFFFFu);
-            const u32 cur = isM ? bbpos : (isI ? s_ins + s_carry_i + (ex_s >> 16) : NIL);
-            s_cur[tid] = cur;
-            __syncthreads();
-            const u32 prev = ex_m ? s_cur[ex_m - 1] : s_last;
-            const u32 ecur = s_ecur;
-            // vertex side of addAln
-            if (isM || isD) {
-                cov[bbpos]++;                                    // _g[_bbMap[curr]].coverage++
-                N[bbpos].bfv = (N[bbpos].bfv & ~0xFFu) | tch;    // .base = targetBase
-                if (isM) N[bbpos].weight++;
-            } else if (isI) {
-                Node nd;
-                nd.in_head = NIL; nd.out_head = NIL; nd.deg = 0; nd.weight = 1; nd.bbmap = bbpos;
-                nd.bfv = q; nd.cnt = 0; nd.best = NIL;
-                N[cur] = nd;
+        for (u32 c0 = 0; c0 < n; c0 += TILE) {
+            const u32 cb = c0 + tid * CPT;
+            u32 q[CPT], tc[CPT], kind[CPT];  // kind: 0 none, 1 match, 2 deletion, 3 insertion
+            u32 nadv = 0, nins = 0, lastp = 0;
+#pragma unroll
+            for (int j = 0; j < CPT; j++) {
+                kind[j] = 0; q[j] = 0; tc[j] = 0;
+                if (cb + j < n) {
+                    const u32 col = cols[cb + j];
+                    q[j] = col & 0xFFu; tc[j] = col >> 8;
+                    // column classes exactly as addAln tests them (:75, :84, :93)
+                    if (q[j] == tc[j]) kind[j] = 1;
+                    else if (q[j] == DASH) kind[j] = 2;
+                    else if (tc[j] == DASH) kind[j] = 3;
+                }
+                if (kind[j] == 1 || kind[j] == 2) nadv++;
+                if (kind[j] == 3) nins++;
+                if (kind[j] == 1 || kind[j] == 3) lastp = tid * CPT + j + 1;
             }
-            // addEdge(prev, cur): does the edge exist?
-            u32 exist = NIL;
-            bool need_new = false;
-            if (path) {
-                if (isM && prev <= L && cur == prev + 1) exist = prev;         // ctor edge prev -> prev+1
-                else if (isI || prev >= L + 2) need_new = true;                // touches a fresh vertex
-                else {
-                    exist = prev == ENTER ? find_in(N, E, cur, ENTER) : find_out(N, E, prev, cur);
-                    need_new = exist == NIL;
+            u32 ex_s, ex_m, tot_s, tot_m;
+            block_scan2(nadv | (nins << 16), lastp, ex_s, ex_m, tot_s, tot_m, sa, sb);
+            u32 bbpos[CPT], cur[CPT];
+            {
+                u32 tb = start + s_carry_t + (ex_s & 0xFFFFu), ib = s_ins + s_carry_i + (ex_s >> 16);
+#pragma unroll
+                for (int j = 0; j < CPT; j++) {
+                    bbpos[j] = tb;
+                    cur[j] = kind[j] == 1 ? tb : (kind[j] == 3 ? ib : NIL);
+                    if (kind[j] == 1 || kind[j] == 2) tb++;
+                    if (kind[j] == 3) ib++;
+                    s_cur[tid * CPT + j] = cur[j];
+                }
+            }
+            __syncthreads();
+            u32 prev = ex_m ? s_cur[ex_m - 1] : s_last;
+            const u32 ecur = s_ecur;
+            // vertex side of addAln + classification of addEdge(prev, cur)
+            u32 exist[CPT], pv[CPT], nnew = 0;
+#pragma unroll
+            for (int j = 0; j < CPT; j++) {
+                exist[j] = NIL; pv[j] = NIL;
+                const u32 p = bbpos[j];
+                if (kind[j] == 1 || kind[j] == 2) {
+                    accCov[p]++;                 // _g[_bbMap[curr]].coverage++
+                    accB[p] = (u16)tc[j];        // .base = targetBase (last alignment in order wins)
+                    if (kind[j] == 1) accW[p]++;
+                } else if (kind[j] == 3) {
+                    Node nd;
+                    nd.in_head = NIL; nd.out_head = NIL; nd.deg = 0; nd.weight = 1; nd.bbmap = p;
+                    nd.bfv = q[j]; nd.cnt = 0; nd.best = NIL;
+                    N[cur[j]] = nd;
+                }
+                if (kind[j] == 1 || kind[j] == 3) {
+                    pv[j] = prev;
+                    if (kind[j] == 1 && prev <= L && cur[j] == prev + 1) accC[prev]++;   // ctor edge prev -> prev+1
+                    else if (kind[j] == 3 || prev >= L + 2) { exist[j] = NIL - 1; nnew++; }   // touches a fresh vertex
+                    else {
+                        const u32 e = prev == ENTER ? find_in(N, E, cur[j], ENTER) : find_out(N, E, prev, cur[j]);
+                        if (e == NIL) { exist[j] = NIL - 1; nnew++; } else exist[j] = e;
+                    }
+                    prev = cur[j];
                 }
             }
             u32 ex_e, d0, tot_e, d1;
-            block_scan2(need_new ? 1u : 0u, 0u, ex_e, d0, tot_e, d1, sa, sb);  // also orders the vertex writes
-            if (exist != NIL) E[exist].count++;
-            if (need_new) {
-                const u32 e = ecur + ex_e;
-                E[e].src = prev; E[e].dst = cur; E[e].count = 1; E[e].visited = 0;
-                E[e].next_out = NIL; E[e].next_in = NIL;
-                list_append_out(N, E, prev, e);
-                list_append_in(N, E, cur, e);
-                atomicAdd(&N[prev].deg, 0x10000u);
-                atomicAdd(&N[cur].deg, 1u);
+            block_scan2(nnew, 0u, ex_e, d0, tot_e, d1, sa, sb);  // also orders the vertex writes
+            u32 e = ecur + ex_e;
+#pragma unroll
+            for (int j = 0; j < CPT; j++) {
+                if (exist[j] == NIL - 1) {
+                    Edge ed;
+                    ed.src = pv[j]; ed.dst = cur[j]; ed.count = 1; ed.visited = 0;
+                    ed.next_out = NIL; ed.prev_out = e; ed.next_in = NIL; ed.prev_in = e;
+                    E[e] = ed;
+                    list_append_out(N, E, pv[j], e);
+                    list_append_in(N, E, cur[j], e);
+                    atomicAdd(&N[pv[j]].deg, 0x10000u);
+                    atomicAdd(&N[cur[j]].deg, 1u);
+                    e++;
+                } else if (exist[j] != NIL) {
+                    E[exist[j]].count++;
+                }
             }
             __syncthreads();
             if (tid == 0) {
@@ -446,22 +491,35 @@ __global__ void __launch_bounds__(BT) k_build_graph(BuildArgs a) {
         }
         if (tid == 0) {  // addEdge(prevVtx, _exitVtx) :106
             const u32 prev = s_last;
-            u32 exist = NIL;
-            if (prev == L) exist = L;
-            else if (prev < L + 2) exist = find_out(N, E, prev, EXIT);
-            if (exist != NIL) E[exist].count++;
+            u32 ex = NIL;
+            if (prev == L) accC[L]++;
             else {
-                const u32 e = s_ecur++;
-                E[e].src = prev; E[e].dst = EXIT; E[e].count = 1; E[e].visited = 0;
-                E[e].next_out = NIL; E[e].next_in = NIL;
-                list_append_out(N, E, prev, e);
-                list_append_in(N, E, EXIT, e);
-                N[prev].deg += 0x10000u;
-                N[EXIT].deg += 1u;
+                if (prev < L + 2) ex = find_out(N, E, prev, EXIT);
+                if (ex != NIL) E[ex].count++;
+                else {
+                    const u32 e = s_ecur++;
+                    Edge ed;
+                    ed.src = prev; ed.dst = EXIT; ed.count = 1; ed.visited = 0;
+                    ed.next_out = NIL; ed.prev_out = e; ed.next_in = NIL; ed.prev_in = e;
+                    E[e] = ed;
+                    list_append_out(N, E, prev, e);
+                    list_append_in(N, E, EXIT, e);
+                    N[prev].deg += 0x10000u;
+                    N[EXIT].deg += 1u;
+                }
             }
             s_ins += s_carry_i;
         }
         __syncthreads();
+    }
+    // fold the accumulators into the records
+    for (u32 p = tid; p <= L + 1; p += BT) {
+        const u32 cv = accCov[p];
+        cov[p] = (int)cv;
+        if (cv) N[p].bfv = (N[p].bfv & ~0xFFu) | (accB[p] & 0xFFu);
+        const u32 w = accW[p];
+        if (w) N[p].weight += (int)w;
+        if (p <= L) { const u32 cc = accC[p]; if (cc) E[p].count = (int)cc; }
     }
     if (tid == 0) { a.tgt_ne[t] = s_ecur; a.tgt_nv[t] = s_ins; }
 }
@@ -684,28 +742,153 @@ __device__ void g_merge_out(TCtx& c, u32 n) {
     }
 }
 
+// ---- lean fast paths.  The serial kernels are instruction-issue bound (ncu, round 1: 385
+// instructions per popped vertex, 1 active lane), so the common case -- a vertex whose
+// neighbourhood needs no merge -- is handled with 128-bit loads of the record halves and a
+// neighbour snapshot in shared memory that the visited-marking loop reuses.
+__device__ __forceinline__ uint4 ld4(const void* p) { return *reinterpret_cast<const uint4*>(p); }
+#define NODE_A(N, v) ld4(&(N)[v])                           // deg, bfv, in_head, out_head
+#define NODE_B(N, v) ld4(((const uint4*)&(N)[v]) + 1)       // weight, bbmap, score|cnt, best
+#define EDGE_A(E, e) ld4(&(E)[e])                           // src, dst, count, visited
+#define EDGE_B(E, e) ld4(((const uint4*)&(E)[e]) + 1)       // next_out, prev_out, next_in, prev_in
+
+#define MAXK 62  // neighbours snapshotted on the fast path (4 arrays + an 8-word bitmap = 256 words)
+#define TOO_BIG 0xFFFFFFFFu
+
+// out-neighbourhood of u: se = edge id | visited << 31, sd = target, sx = target bfv, sy = target deg
+__device__ __forceinline__ u32 scan_out(const Node* N, const Edge* E, u32 head, u32* se, u32* sd, u32* sx, u32* sy) {
+    u32 cnt = 0;
+    for (u32 e = head; e != NIL;) {
+        const uint4 ea = EDGE_A(E, e);
+        const u32 nx = E[e].next_out;
+        const uint4 da = NODE_A(N, ea.y);
+        if (cnt >= MAXK) return TOO_BIG;
+        se[cnt] = e | (ea.w ? 0x80000000u : 0u); sd[cnt] = ea.y; sx[cnt] = da.y; sy[cnt] = da.x;
+        cnt++;
+        e = nx;
+    }
+    return cnt;
+}
+__device__ __forceinline__ bool bitmap_test_set(u32* bm, u32 b) {
+    const u32 w = b >> 5, m = 1u << (b & 31);
+    const u32 old = bm[w];
+    bm[w] = old | m;
+    return old & m;
+}
+// does any std::map group of mergeOutNodes(u) hold more than one vertex?
+__device__ __forceinline__ bool out_group_exists(u32 cnt, const u32* sx, const u32* sy, u32* bm) {
+    u32 elig = 0;
+    for (u32 i = 0; i < cnt; i++) elig += (sy[i] & 0xFFFFu) == 1;
+    if (elig < 2) return false;
+#pragma unroll
+    for (int w = 0; w < 8; w++) bm[w] = 0;
+    for (u32 i = 0; i < cnt; i++)
+        if ((sy[i] & 0xFFFFu) == 1 && bitmap_test_set(bm, sx[i] & 0xFFu)) return true;
+    return false;
+}
+// same question for mergeInNodes(n): predecessors with out_degree 1 sharing a base
+__device__ __forceinline__ bool in_group_exists(const Node* N, const Edge* E, u32 in_head, u32* bm) {
+#pragma unroll
+    for (int w = 0; w < 8; w++) bm[w] = 0;
+    for (u32 e = in_head; e != NIL;) {
+        const u32 s = E[e].src, nx = E[e].next_in;
+        const uint4 sa = NODE_A(N, s);
+        if ((sa.x >> 16) == 1 && bitmap_test_set(bm, sa.y & 0xFFu)) return true;
+        e = nx;
+    }
+    return false;
+}
+
+// mergeOutNodes :217-267 driven by the shared-memory snapshot (same groups, same order)
+__device__ void g_merge_out_snap(TCtx& c, u32 cnt, const u32* sd, const u32* sx, const u32* sy) {
+    Node* N = c.N;
+    Edge* E = c.E;
+    int last = -129;
+    while (c.status == T_OK) {
+        int key = 1000;
+        for (u32 i = 0; i < cnt; i++) {
+            if ((sy[i] & 0xFFFFu) != 1) continue;
+            const int b = (int)(signed char)(sx[i] & 0xFFu);
+            if (b > last && b < key) key = b;
+        }
+        if (key == 1000) break;
+        last = key;
+        u32 an = NIL, members = 0;
+        for (u32 i = 0; i < cnt; i++)
+            if ((sy[i] & 0xFFFFu) == 1 && (int)(signed char)(sx[i] & 0xFFu) == key) { if (an == NIL) an = sd[i]; members++; }
+        if (members < 2) continue;
+        const u32 an_in = N[an].in_head;
+        for (u32 i = 0; i < cnt; i++) {
+            const u32 ni = sd[i];
+            if (ni == an || (sy[i] & 0xFFFFu) != 1 || (int)(signed char)(sx[i] & 0xFFu) != key) continue;
+            E[an_in].count += E[N[ni].in_head].count;
+            N[an].weight += N[ni].weight;
+        }
+        for (u32 i = 0; i < cnt; i++) {
+            const u32 ni = sd[i];
+            if (ni == an || (sy[i] & 0xFFFFu) != 1 || (int)(signed char)(sx[i] & 0xFFu) != key) continue;
+            for (u32 oe = N[ni].out_head; oe != NIL; oe = E[oe].next_out) {
+                const uint4 oa = EDGE_A(E, oe);
+                const u32 e = find_out(N, E, an, oa.y);
+                if (e != NIL) E[e].count += (int)oa.z;
+                else g_add_edge(c, an, oa.y, (int)oa.z, oa.w);
+            }
+            g_reap(c, ni);
+        }
+    }
+}
+
 // mergeNodes :129-160
 __device__ void g_merge_nodes(TCtx& c, u32 ENTER) {
     Node* N = c.N;
     Edge* E = c.E;
+    u32* se = c.S;
+    u32* sd = se + MAXK;
+    u32* sx = sd + MAXK;
+    u32* sy = sx + MAXK;
+    u32* bm = sy + MAXK;
     u32 head = ENTER, tail = ENTER;
     N[ENTER].best = NIL;
     N[ENTER].bfv |= NF_QUEUED << 8;
     while (head != NIL && c.status == T_OK) {
         const u32 u = head;
-        g_merge_in(c, u);
-        g_merge_out(c, u);
-        for (u32 e = N[u].out_head; e != NIL; e = E[e].next_out) {
-            const u32 v = E[e].dst;
-            if (!E[e].visited) { E[e].visited = 1; N[v].bfv += 0x10000u; }
-            const u32 bfv = N[v].bfv;
-            if (n_vis(bfv) == n_in_deg(N[v])) {  // notVisited == 0
-                if (n_flags(bfv) & NF_QUEUED) { c.status = T_INTERNAL; break; }
-                N[v].bfv = bfv | (NF_QUEUED << 8);
-                N[v].best = NIL;
-                N[tail].best = v;
+        uint4 a = NODE_A(N, u);
+        if ((a.x & 0xFFFFu) >= 2 && in_group_exists(N, E, a.z, bm)) {
+            g_merge_in(c, u);
+            a = NODE_A(N, u);
+        }
+        u32 cnt = a.w == NIL ? 0u : scan_out(N, E, a.w, se, sd, sx, sy);
+        if (cnt == TOO_BIG) {  // very wide vertex (enter, exit's predecessors): generic path
+            g_merge_out(c, u);
+            for (u32 e = N[u].out_head; e != NIL; e = E[e].next_out) {
+                const u32 v = E[e].dst;
+                if (!E[e].visited) { E[e].visited = 1; N[v].bfv += 0x10000u; }
+                const u32 bfv = N[v].bfv;
+                if (n_vis(bfv) == n_in_deg(N[v])) {  // notVisited == 0
+                    if (n_flags(bfv) & NF_QUEUED) { c.status = T_INTERNAL; break; }
+                    N[v].bfv = bfv | (NF_QUEUED << 8);
+                    N[tail].best = v;
+                    tail = v;
+                }
+            }
+            head = N[u].best;
+            continue;
+        }
+        if (cnt >= 2 && out_group_exists(cnt, sx, sy, bm)) {
+            g_merge_out_snap(c, cnt, sd, sx, sy);
+            cnt = scan_out(N, E, N[u].out_head, se, sd, sx, sy);  // merging only removes out-edges of u
+        }
+        for (u32 i = 0; i < cnt; i++) {
+            const u32 ev = se[i], v = sd[i];
+            u32 bfv = sx[i];
+            if (!(ev >> 31)) { E[ev].visited = 1; bfv += 0x10000u; }
+            if ((bfv >> 16) == (sy[i] & 0xFFFFu)) {  // notVisited == 0
+                if (bfv & (NF_QUEUED << 8)) { c.status = T_INTERNAL; break; }
+                bfv |= NF_QUEUED << 8;
+                N[tail].best = v;   // N[v].best is still NIL from the build
                 tail = v;
             }
+            if (bfv != sx[i]) N[v].bfv = bfv;
         }
         head = N[u].best;
     }
@@ -735,7 +918,7 @@ __device__ __forceinline__ bool serial_setup(const SerialArgs& a, u32& t, TCtx& 
 }
 
 #define SERIAL_THREADS 128
-#define SERIAL_SMEM_WORDS 4096  // 16 KB per block: 1024 words per worker at tpw=1
+#define SERIAL_SMEM_WORDS 4096  // 16 KB per block: 1024 words per worker at tpw=1, 256 at tpw=4
 
 __global__ void __launch_bounds__(SERIAL_THREADS) k_merge_nodes(SerialArgs a) {
     __shared__ u32 smem[SERIAL_SMEM_WORDS];
@@ -749,10 +932,9 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_merge_nodes(SerialArgs a) {
 
 // bestPath :375-459 and the two consensus() forms :285-373
 __global__ void __launch_bounds__(SERIAL_THREADS) k_best_path(SerialArgs a) {
-    __shared__ u32 smem[SERIAL_SMEM_WORDS];
     u32 t;
     TCtx c;
-    if (!serial_setup(a, t, c, smem, SERIAL_SMEM_WORDS)) return;
+    if (!serial_setup(a, t, c, nullptr, SERIAL_SMEM_WORDS)) return;
     Node* N = c.N;
     Edge* E = c.E;
     const int* cov = a.cov + a.cov_off[t];
@@ -762,30 +944,35 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_best_path(SerialArgs a) {
     N[EXIT].best = NIL;
     while (head != NIL) {
         const u32 n = head;
+        const uint4 na = NODE_A(N, n);
         float best_score = -FLT_MAX;
         u32 best_e = NIL;
-        for (u32 e = N[n].out_head; e != NIL; e = E[e].next_out) {
-            const u32 o = E[e].dst;
-            const Node on = N[o];
-            const float sc = on.score;
+        for (u32 e = na.w; e != NIL;) {
+            const uint4 ea = EDGE_A(E, e);
+            const u32 nx = E[e].next_out;
+            const uint4 oa = NODE_A(N, ea.y);
+            const uint4 ob = NODE_B(N, ea.y);
+            const float sc = __uint_as_float(ob.z);
             float ns;
-            if ((n_flags(on.bfv) & NF_BACKBONE) && on.weight == 1) ns = __fsub_rn(sc, 10.0f);
-            else ns = __fadd_rn(__fsub_rn((float)E[e].count, __fmul_rn((float)cov[on.bbmap], 0.5f)), sc);
+            if ((oa.y & (NF_BACKBONE << 8)) && (int)ob.x == 1) ns = __fsub_rn(sc, 10.0f);
+            else ns = __fadd_rn(__fsub_rn((float)(int)ea.z, __fmul_rn((float)cov[ob.y], 0.5f)), sc);
             if (ns > best_score) { best_score = ns; best_e = e; }
+            e = nx;
         }
-        for (u32 e = N[n].in_head; e != NIL; e = E[e].next_in) {
-            const u32 s = E[e].src;
-            const int k = ++N[s].cnt;
-            if ((u32)k == n_out_deg(N[s])) {  // all out-edges visited
+        for (u32 e = na.z; e != NIL;) {
+            const u32 s = E[e].src, nx = E[e].next_in;
+            const u32 k = (u32)(++N[s].cnt);
+            if (k == (N[s].deg >> 16)) {  // all out-edges visited
                 N[s].best = NIL;
                 N[tail].best = s;
                 tail = s;
             }
+            e = nx;
         }
         const u32 nx = N[n].best;
         N[n].score = best_e != NIL ? best_score : 0.0f;  // absent map key reads as 0.0f (:401)
         N[n].best = best_e;
-        N[n].bfv |= NF_SCORED << 8;
+        N[n].bfv = na.y | (NF_SCORED << 8);
         head = nx;
     }
     // walk the best path and cut it into min-weight runs
@@ -799,12 +986,14 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_best_path(SerialArgs a) {
     bool met = false;
     u32 nfrag = 0, steps = 0, prev = ENTER, status = T_OK;
     for (;;) {
-        const Node nd = N[prev];
-        const u32 b = n_base(nd.bfv);
+        const uint4 pa = NODE_A(N, prev);
+        const uint4 pb = NODE_B(N, prev);
+        const u32 b = pa.y & 0xFFu;
+        const int w = (int)pb.x;
         if (b != eb && b != xb) {
             cons[idx] = (u8)b;
-            if (!met && nd.weight >= minw) { offs = idx; met = true; }
-            else if (met && nd.weight < minw) {
+            if (!met && w >= minw) { offs = idx; met = true; }
+            else if (met && w < minw) {
                 met = false;
                 if (single) { if (idx - offs > length) { best_offs = offs; length = idx - offs; } }
                 else if ((u32)(idx - offs) >= a.min_len) {
@@ -813,8 +1002,8 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_best_path(SerialArgs a) {
             }
             idx++;
         }
-        if (!(n_flags(nd.bfv) & NF_SCORED) || nd.best == NIL) break;
-        prev = E[nd.best].dst;
+        if (!(pa.y & (NF_SCORED << 8)) || pb.w == NIL) break;
+        prev = E[pb.w].dst;
         if (++steps > nV) { status = T_INTERNAL; break; }
     }
     if (single) {
