@@ -755,19 +755,33 @@ __device__ __forceinline__ uint4 ld4(const void* p) { return *reinterpret_cast<c
 #define MAXK 62  // neighbours snapshotted on the fast path (4 arrays + an 8-word bitmap = 256 words)
 #define TOO_BIG 0xFFFFFFFFu
 
-// out-neighbourhood of u: se = edge id | visited << 31, sd = target, sx = target bfv, sy = target deg
-__device__ __forceinline__ u32 scan_out(const Node* N, const Edge* E, u32 head, u32* se, u32* sd, u32* sx, u32* sy) {
-    u32 cnt = 0;
+// One pass over the out-list of u: se = edge id | visited << 31, sd = target, sx = target bfv,
+// sy = target deg.  While at it, find the bases that occur more than once among the merge
+// candidates (targets with in_degree 1): dup_lo/dup_hi are bitmaps over base 0..63 / 64..127.
+// Bases >= 128 (negative as `char`, sorted first by std::map<char,...>) set `weird` and send the
+// vertex down the generic path.
+struct OutScan { u32 cnt; u64 dup_lo, dup_hi; bool weird; };
+__device__ __forceinline__ OutScan scan_out(const Node* N, const Edge* E, u32 head, u32* se, u32* sd, u32* sx, u32* sy) {
+    OutScan r;
+    r.cnt = 0; r.dup_lo = 0; r.dup_hi = 0; r.weird = false;
+    u64 seen_lo = 0, seen_hi = 0;
     for (u32 e = head; e != NIL;) {
         const uint4 ea = EDGE_A(E, e);
         const u32 nx = E[e].next_out;
         const uint4 da = NODE_A(N, ea.y);
-        if (cnt >= MAXK) return TOO_BIG;
-        se[cnt] = e | (ea.w ? 0x80000000u : 0u); sd[cnt] = ea.y; sx[cnt] = da.y; sy[cnt] = da.x;
-        cnt++;
+        if (r.cnt >= MAXK) { r.cnt = TOO_BIG; return r; }
+        se[r.cnt] = e | (ea.w ? 0x80000000u : 0u); sd[r.cnt] = ea.y; sx[r.cnt] = da.y; sy[r.cnt] = da.x;
+        r.cnt++;
+        if ((da.x & 0xFFFFu) == 1) {
+            const u32 b = da.y & 0xFFu;
+            const u64 m = 1ull << (b & 63);
+            if (b < 64) { r.dup_lo |= seen_lo & m; seen_lo |= m; }
+            else if (b < 128) { r.dup_hi |= seen_hi & m; seen_hi |= m; }
+            else r.weird = true;
+        }
         e = nx;
     }
-    return cnt;
+    return r;
 }
 __device__ __forceinline__ bool bitmap_test_set(u32* bm, u32 b) {
     const u32 w = b >> 5, m = 1u << (b & 31);
@@ -775,66 +789,49 @@ __device__ __forceinline__ bool bitmap_test_set(u32* bm, u32 b) {
     bm[w] = old | m;
     return old & m;
 }
-// does any std::map group of mergeOutNodes(u) hold more than one vertex?
-__device__ __forceinline__ bool out_group_exists(u32 cnt, const u32* sx, const u32* sy, u32* bm) {
-    u32 elig = 0;
-    for (u32 i = 0; i < cnt; i++) elig += (sy[i] & 0xFFFFu) == 1;
-    if (elig < 2) return false;
-#pragma unroll
-    for (int w = 0; w < 8; w++) bm[w] = 0;
-    for (u32 i = 0; i < cnt; i++)
-        if ((sy[i] & 0xFFFFu) == 1 && bitmap_test_set(bm, sx[i] & 0xFFu)) return true;
-    return false;
-}
-// same question for mergeInNodes(n): predecessors with out_degree 1 sharing a base
-__device__ __forceinline__ bool in_group_exists(const Node* N, const Edge* E, u32 in_head, u32* bm) {
-#pragma unroll
-    for (int w = 0; w < 8; w++) bm[w] = 0;
+// does any std::map group of mergeInNodes(n) hold more than one vertex (predecessors with
+// out_degree 1 sharing a base)?
+__device__ __forceinline__ bool in_group_exists(const Node* N, const Edge* E, u32 in_head) {
+    u64 seen_lo = 0, seen_hi = 0;
+    bool found = false;
     for (u32 e = in_head; e != NIL;) {
         const u32 s = E[e].src, nx = E[e].next_in;
         const uint4 sa = NODE_A(N, s);
-        if ((sa.x >> 16) == 1 && bitmap_test_set(bm, sa.y & 0xFFu)) return true;
+        if ((sa.x >> 16) == 1) {
+            const u32 b = sa.y & 0xFFu;
+            const u64 m = 1ull << (b & 63);
+            if (b < 64) { found |= (seen_lo & m) != 0; seen_lo |= m; }
+            else if (b < 128) { found |= (seen_hi & m) != 0; seen_hi |= m; }
+            else found = true;  // let the generic code sort it out
+        }
         e = nx;
     }
-    return false;
+    return found;
 }
 
-// mergeOutNodes :217-267 driven by the shared-memory snapshot (same groups, same order)
-__device__ void g_merge_out_snap(TCtx& c, u32 cnt, const u32* sd, const u32* sx, const u32* sy) {
+// mergeOutNodes :217-267 for one std::map key, driven by the shared-memory snapshot.  The two
+// loops of the reference (sum counts/weights, then move edges and reap) touch disjoint state
+// per merged vertex, so they are fused.
+__device__ __forceinline__ void merge_out_group(TCtx& c, u32 key, u32 cnt, const u32* sd, const u32* sx, const u32* sy) {
     Node* N = c.N;
     Edge* E = c.E;
-    int last = -129;
-    while (c.status == T_OK) {
-        int key = 1000;
-        for (u32 i = 0; i < cnt; i++) {
-            if ((sy[i] & 0xFFFFu) != 1) continue;
-            const int b = (int)(signed char)(sx[i] & 0xFFu);
-            if (b > last && b < key) key = b;
+    u32 an = NIL, an_in = NIL;
+    for (u32 i = 0; i < cnt; i++) {
+        if ((sy[i] & 0xFFFFu) != 1 || (sx[i] & 0xFFu) != key) continue;
+        const u32 ni = sd[i];
+        if (an == NIL) { an = ni; an_in = N[an].in_head; continue; }
+        const uint4 nia = NODE_A(N, ni);
+        E[an_in].count += E[nia.z].count;
+        N[an].weight += N[ni].weight;
+        for (u32 oe = nia.w; oe != NIL;) {
+            const uint4 oa = EDGE_A(E, oe);
+            const u32 nx = E[oe].next_out;
+            const u32 e = find_out(N, E, an, oa.y);
+            if (e != NIL) E[e].count += (int)oa.z;
+            else g_add_edge(c, an, oa.y, (int)oa.z, oa.w);
+            oe = nx;
         }
-        if (key == 1000) break;
-        last = key;
-        u32 an = NIL, members = 0;
-        for (u32 i = 0; i < cnt; i++)
-            if ((sy[i] & 0xFFFFu) == 1 && (int)(signed char)(sx[i] & 0xFFu) == key) { if (an == NIL) an = sd[i]; members++; }
-        if (members < 2) continue;
-        const u32 an_in = N[an].in_head;
-        for (u32 i = 0; i < cnt; i++) {
-            const u32 ni = sd[i];
-            if (ni == an || (sy[i] & 0xFFFFu) != 1 || (int)(signed char)(sx[i] & 0xFFu) != key) continue;
-            E[an_in].count += E[N[ni].in_head].count;
-            N[an].weight += N[ni].weight;
-        }
-        for (u32 i = 0; i < cnt; i++) {
-            const u32 ni = sd[i];
-            if (ni == an || (sy[i] & 0xFFFFu) != 1 || (int)(signed char)(sx[i] & 0xFFu) != key) continue;
-            for (u32 oe = N[ni].out_head; oe != NIL; oe = E[oe].next_out) {
-                const uint4 oa = EDGE_A(E, oe);
-                const u32 e = find_out(N, E, an, oa.y);
-                if (e != NIL) E[e].count += (int)oa.z;
-                else g_add_edge(c, an, oa.y, (int)oa.z, oa.w);
-            }
-            g_reap(c, ni);
-        }
+        g_reap(c, ni);
     }
 }
 
@@ -846,19 +843,20 @@ __device__ void g_merge_nodes(TCtx& c, u32 ENTER) {
     u32* sd = se + MAXK;
     u32* sx = sd + MAXK;
     u32* sy = sx + MAXK;
-    u32* bm = sy + MAXK;
     u32 head = ENTER, tail = ENTER;
     N[ENTER].best = NIL;
     N[ENTER].bfv |= NF_QUEUED << 8;
     while (head != NIL && c.status == T_OK) {
         const u32 u = head;
         uint4 a = NODE_A(N, u);
-        if ((a.x & 0xFFFFu) >= 2 && in_group_exists(N, E, a.z, bm)) {
+        if ((a.x & 0xFFFFu) >= 2 && in_group_exists(N, E, a.z)) {
             g_merge_in(c, u);
             a = NODE_A(N, u);
         }
-        u32 cnt = a.w == NIL ? 0u : scan_out(N, E, a.w, se, sd, sx, sy);
-        if (cnt == TOO_BIG) {  // very wide vertex (enter, exit's predecessors): generic path
+        OutScan sc;
+        sc.cnt = 0; sc.dup_lo = 0; sc.dup_hi = 0; sc.weird = false;
+        if (a.w != NIL) sc = scan_out(N, E, a.w, se, sd, sx, sy);
+        if (sc.cnt == TOO_BIG || sc.weird) {  // very wide vertex (enter) or exotic bases: generic path
             g_merge_out(c, u);
             for (u32 e = N[u].out_head; e != NIL; e = E[e].next_out) {
                 const u32 v = E[e].dst;
@@ -874,11 +872,13 @@ __device__ void g_merge_nodes(TCtx& c, u32 ENTER) {
             head = N[u].best;
             continue;
         }
-        if (cnt >= 2 && out_group_exists(cnt, sx, sy, bm)) {
-            g_merge_out_snap(c, cnt, sd, sx, sy);
-            cnt = scan_out(N, E, N[u].out_head, se, sd, sx, sy);  // merging only removes out-edges of u
+        if (sc.dup_lo | sc.dup_hi) {
+            // groups in ascending key order, as std::map<char, ...> iterates them
+            for (u64 m = sc.dup_lo; m && c.status == T_OK; m &= m - 1) merge_out_group(c, (u32)__ffsll((long long)m) - 1, sc.cnt, sd, sx, sy);
+            for (u64 m = sc.dup_hi; m && c.status == T_OK; m &= m - 1) merge_out_group(c, 63u + (u32)__ffsll((long long)m), sc.cnt, sd, sx, sy);
+            sc = scan_out(N, E, N[u].out_head, se, sd, sx, sy);  // merging only removed out-edges of u
         }
-        for (u32 i = 0; i < cnt; i++) {
+        for (u32 i = 0; i < sc.cnt; i++) {
             const u32 ev = se[i], v = sd[i];
             u32 bfv = sx[i];
             if (!(ev >> 31)) { E[ev].visited = 1; bfv += 0x10000u; }
