@@ -259,15 +259,15 @@ def run_gpu(args):
     def e2e_pass():
         nb = 0
         d2h = 0
-        eng.submit(sub_pb[0])
-        for i in range(1, len(sub_pb)):
-            eng.submit(sub_pb[i])
+        nsub, sent, got = len(sub_pb), 0, 0
+        while got < nsub:
+            while sent < nsub and sent - got < api.MAX_INFLIGHT:
+                eng.submit(sub_pb[sent])
+                sent += 1
             r = eng.collect(copy=False)
+            got += 1
             nb += int(np.ctypeslib.as_array(r.frag_seq_len, (r.n_frags,)).astype(np.int64).sum()) if r.n_frags else 0
             d2h += int(r.seq_bytes) + 8 * r.n_frags + 16 * r.n_targets
-        r = eng.collect(copy=False)
-        nb += int(np.ctypeslib.as_array(r.frag_seq_len, (r.n_frags,)).astype(np.int64).sum()) if r.n_frags else 0
-        d2h += int(r.seq_bytes) + 8 * r.n_frags + 16 * r.n_targets
         return nb, d2h
 
     for _ in range(max(1, args.warmup - 1)):
@@ -350,7 +350,7 @@ def main():
     ap.add_argument("--L", type=int, default=8000)
     ap.add_argument("--cov", type=float, default=30)
     ap.add_argument("--seed", type=int, default=2)
-    ap.add_argument("--sub", type=int, default=1250, help="targets per submitted sub-batch (e2e arm)")
+    ap.add_argument("--sub", type=int, default=2500, help="targets per submitted sub-batch (e2e arm)")
     ap.add_argument("--tpw", type=int, default=0, help="targets per warp in the serial kernels (0 = auto)")
     ap.add_argument("--scratch-gb", type=int, default=48)
     ap.add_argument("--no-cpu", action="store_true")

@@ -23,6 +23,7 @@ extern "C" {
 #endif
 
 #define DGC_ABI_VERSION 1
+#define DGC_MAX_INFLIGHT 4 /* batches that may be submitted and not yet collected */
 
 /* error codes (function return values) */
 #define DGC_OK 0
@@ -121,8 +122,9 @@ int dgc_host_free(void* p);
 
 /* Asynchronous pipeline: submit copies the batch H2D and enqueues the kernels on one of the
  * handle's streams (the caller's buffers must stay untouched until the matching collect);
- * collect returns results in submit order.  Replaces AlnBuf::push / CnsBuf::pop
- * (main.cpp:87,120,144,168). */
+ * collect returns results in submit order.  At most DGC_MAX_INFLIGHT batches may be in flight
+ * (submit returns DGC_E_STATE beyond that); their kernels and copies overlap on separate streams.
+ * Replaces AlnBuf::push / CnsBuf::pop (main.cpp:87,120,144,168). */
 int dgc_submit(dgc_handle* h, const dgc_batch* batch);
 int dgc_collect(dgc_handle* h, dgc_results* out);
 

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libdagcon_b200.so")
 
 T_OK, T_SKIPPED, T_BAD_ALIGNMENT, T_TOO_MANY_ALNS, T_INTERNAL = 0, 1, 2, 3, 4
 F_NO_NORMALIZE, F_NO_TRIM, F_NO_MERGE, F_SINGLE = 1, 2, 4, 8
+MAX_INFLIGHT = 4
 
 EXPORTS = ["dgc_abi_version", "dgc_device_count", "dgc_create", "dgc_destroy", "dgc_last_error", "dgc_host_alloc",
            "dgc_host_free", "dgc_submit", "dgc_collect", "dgc_consensus", "dgc_upload", "dgc_run", "dgc_dbatch_free",

@@ -121,7 +121,7 @@ struct Slot {
 
 }  // namespace
 
-#define NSLOT 3
+#define NSLOT (DGC_MAX_INFLIGHT + 1)
 struct dgc_handle {
     dgc_opts opts{};
     int device = 0;

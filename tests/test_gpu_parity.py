@@ -257,13 +257,16 @@ def test_async_submit_collect_order(api, synth):
     pbs = [api.PackedBatch.from_synth(synth.gen_batch(seed=20 + i, L=1200, cov=10, t0=0, nt=8)) for i in range(5)]
     sync = [[eng(pb).frags(t) for t in range(8)] for pb in pbs]
     got = []
-    eng.submit(pbs[0])
-    for i in range(1, 5):
+    for i in range(4):
         eng.submit(pbs[i])
-        r = eng.collect()
-        got.append([r.frags(t) for t in range(8)])
+    with pytest.raises(api.DagconError):
+        eng.submit(pbs[4])          # DGC_MAX_INFLIGHT reached
     r = eng.collect()
     got.append([r.frags(t) for t in range(8)])
+    eng.submit(pbs[4])
+    for i in range(4):
+        r = eng.collect()
+        got.append([r.frags(t) for t in range(8)])
     with pytest.raises(api.DagconError):
         eng.collect()
     eng.close()
