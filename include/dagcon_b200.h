@@ -121,7 +121,8 @@ int dgc_host_alloc(void** p, uint64_t bytes);
 int dgc_host_free(void* p);
 
 /* Asynchronous pipeline: submit copies the batch H2D and enqueues the kernels on one of the
- * handle's streams (the caller's buffers must stay untouched until the matching collect);
+ * handle's streams (the dgc_batch struct is copied; the arrays it points to must stay untouched
+ * until the matching collect);
  * collect returns results in submit order.  At most DGC_MAX_INFLIGHT batches may be in flight
  * (submit returns DGC_E_STATE beyond that); their kernels and copies overlap on separate streams.
  * Replaces AlnBuf::push / CnsBuf::pop (main.cpp:87,120,144,168). */

@@ -114,7 +114,7 @@ struct Slot {
     std::mutex mu;
     std::condition_variable cv;
     enum State { IDLE, QUEUED, RUNNING, DONE, STOP } state = IDLE;
-    const dgc_batch* pending = nullptr;
+    dgc_batch pending{};  // copied at submit: only the arrays it points to must outlive the call
     int rc = 0;
     std::string err;
 };
@@ -499,9 +499,9 @@ void worker_main(Slot* sp) {
         s.cv.wait(lk, [&] { return s.state == Slot::QUEUED || s.state == Slot::STOP; });
         if (s.state == Slot::STOP) return;
         s.state = Slot::RUNNING;
-        const dgc_batch* b = s.pending;
+        const dgc_batch b = s.pending;
         lk.unlock();
-        int rc = slot_process(s, b);
+        int rc = slot_process(s, &b);
         lk.lock();
         s.rc = rc;
         s.state = Slot::DONE;
@@ -617,7 +617,7 @@ int dgc_submit(dgc_handle* h, const dgc_batch* batch) {
     {
         std::unique_lock<std::mutex> lk(s.mu);
         s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
-        s.pending = batch;
+        s.pending = *batch;
         s.state = Slot::QUEUED;
         s.cv.notify_all();
     }

@@ -1,0 +1,180 @@
+// dagcon_host.hpp -- C++ host side above the C ABI (include/dagcon_b200.h).
+//
+// Mirrors the reference's interfaces for this path so that its call sites read the same:
+//   dagcon::Alignment          reference src/cpp/Alignment.hpp:12-42
+//   AlnProvider                reference src/cpp/AlnProvider.hpp:32-46
+//   BlasrM5AlnProvider         reference src/cpp/BlasrM5AlnProvider.hpp (m5 and 'pre' text, grouped by target)
+//   ProgramOpts                reference src/cpp/ProgramOpts.hpp:8-36
+// and replaces the Reader -> BoundedBuffer -> N x Consensus -> BoundedBuffer -> Writer thread pipeline
+// (reference src/cpp/main.cpp:37-176,248-274) with: one scanner thread that cuts the input text into
+// target groups, N packer threads that parse those lines straight into pinned dgc_batch buffers, and one
+// dispatcher thread that deals batches round-robin to the GPUs and gathers the CnsResults in input order.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <exception>
+#include <string>
+#include <vector>
+
+#include "../../include/dagcon_b200.h"
+
+namespace dagcon {
+struct Alignment {
+    uint32_t tlen = 0;   // length of the sequence being corrected
+    uint32_t start = 0;  // 1-based target offset of the first target base
+    uint32_t end = 0;
+    std::string id;      // target id
+    std::string sid;     // supporting read id
+    char strand = '+';
+    std::string qstr, tstr;  // equal-length gapped strings
+};
+}  // namespace dagcon
+
+namespace PacBio {
+namespace DagCon {
+class IOException : public std::exception {
+public:
+    explicit IOException(std::string desc) : desc_(std::move(desc)) {}
+    const char* what() const noexcept override { return desc_.c_str(); }
+
+private:
+    std::string desc_;
+};
+}  // namespace DagCon
+}  // namespace PacBio
+
+namespace M5Exception {
+struct FormatError {
+    std::string msg;
+};
+struct FileOpenError {};
+struct SortError {};
+}  // namespace M5Exception
+
+class AlnProvider {
+public:
+    // Clears dest, fills it with the next target's alignments; false when the input is exhausted
+    // (the last call may still have filled dest).
+    virtual bool nextTarget(std::vector<dagcon::Alignment>& dest) = 0;
+    virtual bool nextTarget(std::string& targSeq, std::vector<dagcon::Alignment>& dest) = 0;
+    virtual ~AlnProvider() {}
+};
+
+namespace dgh {
+
+enum class TextFormat { M5, PRE };
+
+// One input line, already split: views into the line's bytes (no copies).
+struct LineFields {
+    const char* sid = nullptr; size_t sid_len = 0;
+    const char* id = nullptr; size_t id_len = 0;
+    uint32_t tlen = 0, start = 0, end = 0;
+    char strand = '+';
+    const char* q = nullptr; size_t q_len = 0;
+    const char* t = nullptr; size_t t_len = 0;
+};
+
+// Splits on single spaces, skipping empty fields (reference Alignment.cpp:44-55,82-93).
+// m5: id=f[5], tlen=f[6], start=f[7]+1, strand=f[9][0], q=f[16], t=f[18]  (Alignment.cpp:57-79)
+// pre: sid=f[0], id=f[1], strand=f[2][0], tlen=f[3], start=f[4], end=f[5], q=f[6], t=f[7] (:95-111)
+// Returns false on an empty line; throws M5Exception::FormatError on a short or non-numeric line.
+bool split_line(const char* p, size_t n, TextFormat fmt, LineFields& out);
+// Only the target-id field (what the scanner needs to group lines).
+bool line_target_id(const char* p, size_t n, TextFormat fmt, const char*& id, size_t& id_len);
+// revComp of reference Alignment.cpp:15-26: complements upper-case ACGT only, then reverses.
+void revcomp_into(const char* src, size_t n, uint8_t* dst);
+
+// A packed batch in host memory (pinned when `pinned`), laid out as include/dagcon_b200.h: dgc_batch.
+class HostBatch {
+public:
+    HostBatch(bool pinned, size_t arena_cap, size_t aln_cap, size_t tgt_cap);
+    ~HostBatch();
+    HostBatch(const HostBatch&) = delete;
+    HostBatch& operator=(const HostBatch&) = delete;
+
+    void clear();
+    // Appends one target given its lines.  All lines must carry the same target id.
+    void add_target_lines(const std::vector<std::pair<const char*, size_t>>& lines, TextFormat fmt);
+    // Appends one target from provider output (the reference-facing form).
+    void add_target(const std::vector<dagcon::Alignment>& alns, const std::string* backbone = nullptr);
+    dgc_batch view() const;
+
+    uint32_t n_targets = 0, n_alns = 0;
+    uint64_t arena_bytes = 0;
+    bool has_backbone = false;
+    std::vector<std::string> ids;   // Alignment::id of alns[0] per target
+    uint64_t seq = 0;               // position in the input stream (batch number)
+
+    uint32_t* tgt_tlen = nullptr;
+    uint32_t* tgt_aln_begin = nullptr;
+    uint64_t* tgt_bb_off = nullptr;
+    uint32_t* aln_start = nullptr;
+    uint32_t* aln_len = nullptr;
+    uint64_t* aln_q_off = nullptr;
+    uint64_t* aln_t_off = nullptr;
+    uint8_t* arena = nullptr;
+
+private:
+    void* alloc(size_t bytes);
+    void release(void* p);
+    void need_arena(size_t extra);
+    void need_alns(size_t extra);
+    void need_targets(size_t extra);
+    bool pinned_;
+    size_t arena_cap_ = 0, aln_cap_ = 0, tgt_cap_ = 0;
+};
+
+// Options shared by the CLI and the C test hooks (mirror of ProgramOpts + dispatcher knobs).
+struct ProgramOpts {
+    size_t minCov = 6;
+    size_t minLen = 500;
+    unsigned int trim = 50;
+    int threads = 4;        // -j: packer threads here (the reference's consensus threads)
+    bool align = false;     // -a: input is 'pre' and must be aligned first
+    bool verbose = false;
+    std::string input = "-";
+    // dispatcher
+    int gpus = 0;           // 0 = all visible devices
+    size_t batchTargets = 2048;
+    size_t batchBytes = 1ull << 30;
+    bool stats = false;
+};
+
+struct RunStats {
+    uint64_t targets_in = 0, targets_dropped = 0, alignments = 0, input_bytes = 0;
+    uint64_t batches = 0, records = 0, bases = 0;
+    double seconds = 0, scan_seconds = 0;
+};
+
+// Reads `opts.input` ("-" = stdin), runs every target through the GPUs, writes FASTA records to `out`
+// in input-target order.  Returns 0 or a DGC_E_* code (message in `err`).
+int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err);
+
+// The scanner stage alone, for tests and for callers that bring their own dispatcher: cuts the text into
+// batches of whole targets and hands each packed batch to `sink` in input order (sink owns nothing; the
+// batch is recycled after it returns).
+typedef void (*BatchSink)(const HostBatch& batch, void* user);
+int pack_text(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err);
+
+}  // namespace dgh
+
+// Reference-shaped provider over the same line parser (m5 by default, 'pre' when asked).
+class BlasrM5AlnProvider : public AlnProvider {
+public:
+    explicit BlasrM5AlnProvider(const std::string& fpath, dgh::TextFormat fmt = dgh::TextFormat::M5);
+    explicit BlasrM5AlnProvider(FILE* stream, dgh::TextFormat fmt = dgh::TextFormat::M5);
+    ~BlasrM5AlnProvider() override;
+    bool nextTarget(std::vector<dagcon::Alignment>& dest) override;
+    bool nextTarget(std::string& targSeq, std::vector<dagcon::Alignment>& dest) override;
+
+private:
+    bool read_line(dagcon::Alignment& aln, bool& blank);
+    FILE* fp_ = nullptr;
+    bool owns_ = false;
+    dgh::TextFormat fmt_;
+    std::string currId_;
+    bool firstAln_ = true;
+    dagcon::Alignment prevAln_;
+    char* line_ = nullptr;
+    size_t line_cap_ = 0;
+};

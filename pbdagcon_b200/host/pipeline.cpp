@@ -1,0 +1,401 @@
+// pipeline.cpp -- the batched GPU dispatcher that replaces the reference's thread pipeline
+// (reference src/cpp/main.cpp:37-176 Reader / Consensus / Writer, :248-274 thread set-up;
+//  src/cpp/BoundedBuffer.hpp:18-50).
+//
+//   scanner (1 thread)   reads the text in 64 MiB blocks, finds line ends and each line's target id, applies the
+//                        Reader's coverage filter (main.cpp:66-72), cuts the stream into work units of whole targets
+//   packers (-j threads) parse a unit's lines straight into a pinned HostBatch (no per-alignment std::string)
+//   dispatcher (caller)  deals batches round-robin over the GPUs (dgc_submit, <= DGC_MAX_INFLIGHT per GPU),
+//                        collects in input order (dgc_collect) and writes ">id/b_e\nSEQ\n" (main.cpp:139-145)
+#include <unistd.h>
+#include <fcntl.h>
+
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <thread>
+
+#include "dagcon_host.hpp"
+
+namespace dgh {
+namespace {
+
+struct Block {
+    std::unique_ptr<char[]> buf;
+    size_t cap = 0, len = 0;
+};
+
+struct WorkUnit {
+    uint64_t seq = 0;
+    std::vector<std::shared_ptr<Block>> blocks;
+    std::vector<std::pair<const char*, size_t>> lines;
+    std::vector<uint32_t> tgt_begin{0};  // CSR over lines
+    size_t bytes = 0;
+    size_t targets() const { return tgt_begin.size() - 1; }
+};
+
+template <class T>
+class Channel {  // bounded FIFO; close() wakes everybody
+public:
+    explicit Channel(size_t cap) : cap_(cap) {}
+    bool push(T v) {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_space_.wait(lk, [&] { return q_.size() < cap_ || closed_; });
+        if (closed_) return false;
+        q_.push_back(std::move(v));
+        cv_item_.notify_one();
+        return true;
+    }
+    bool pop(T& v) {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_item_.wait(lk, [&] { return !q_.empty() || closed_; });
+        if (q_.empty()) return false;
+        v = std::move(q_.front());
+        q_.pop_front();
+        cv_space_.notify_one();
+        return true;
+    }
+    void close() {
+        std::lock_guard<std::mutex> lk(mu_);
+        closed_ = true;
+        cv_item_.notify_all();
+        cv_space_.notify_all();
+    }
+
+private:
+    std::mutex mu_;
+    std::condition_variable cv_item_, cv_space_;
+    std::deque<T> q_;
+    size_t cap_;
+    bool closed_ = false;
+};
+
+constexpr size_t BLOCK_BYTES = 64u << 20;
+
+class Scanner {
+public:
+    Scanner(const ProgramOpts& o, TextFormat fmt, Channel<std::unique_ptr<WorkUnit>>& out, RunStats& st)
+        : o_(o), fmt_(fmt), out_(out), st_(st) {}
+
+    void run() {
+        int fd = 0;
+        if (o_.input != "-") {
+            fd = open(o_.input.c_str(), O_RDONLY);
+            if (fd < 0) throw M5Exception::FileOpenError();
+        }
+        auto blk = new_block(BLOCK_BYTES);
+        unit_.reset(new WorkUnit());
+        bool eof = false;
+        while (!eof) {
+            while (blk->len < blk->cap) {  // fill the block
+                const ssize_t r = read(fd, blk->buf.get() + blk->len, blk->cap - blk->len);
+                if (r < 0) { if (errno == EINTR) continue; throw PacBio::DagCon::IOException("read error on the alignment input"); }
+                if (r == 0) { eof = true; break; }
+                blk->len += (size_t)r;
+                st_.input_bytes += (uint64_t)r;
+            }
+            const char* p = blk->buf.get();
+            const char* e = p + blk->len;
+            const char* line = p + scanned_;
+            for (;;) {
+                const char* nl = (const char*)memchr(line, '\n', (size_t)(e - line));
+                if (!nl) break;
+                take_line(blk, line, (size_t)(nl - line));
+                line = nl + 1;
+            }
+            if (eof) {
+                if (line < e) take_line(blk, line, (size_t)(e - line));  // last line without '\n'
+                break;
+            }
+            // carry the partial last line into a fresh block (a line is always contiguous in one block)
+            const size_t tail = (size_t)(e - line);
+            auto nb = new_block(std::max(BLOCK_BYTES, 2 * tail + 4096));
+            memcpy(nb->buf.get(), line, tail);
+            nb->len = tail;
+            blk->len -= tail;
+            blk = nb;
+            scanned_ = 0;
+        }
+        close_target();
+        flush_unit();
+        if (fd > 0) close(fd);
+    }
+
+private:
+    std::shared_ptr<Block> new_block(size_t cap) {
+        auto b = std::make_shared<Block>();
+        b->buf.reset(new char[cap]);
+        b->cap = cap;
+        return b;
+    }
+
+    void take_line(const std::shared_ptr<Block>& blk, const char* p, size_t n) {
+        const char* id; size_t idn;
+        if (!line_target_id(p, n, fmt_, id, idn)) { blank_pending_ = true; return; }
+        if (blank_pending_) throw M5Exception::FormatError{"blank line inside the alignment stream"};
+        if (!have_id_ || idn != cur_id_.size() || memcmp(id, cur_id_.data(), idn) != 0) {
+            close_target();
+            cur_id_.assign(id, idn);
+            have_id_ = true;
+        }
+        if (cur_blocks_.empty() || cur_blocks_.back() != blk) cur_blocks_.push_back(blk);
+        cur_lines_.emplace_back(p, n);
+        cur_bytes_ += n;
+    }
+
+    // Reader's filter (main.cpp:66-72): groups with fewer than minCov alignments never reach a consumer.
+    void close_target() {
+        if (cur_lines_.empty()) return;
+        st_.targets_in++;
+        st_.alignments += cur_lines_.size();
+        if (cur_lines_.size() < o_.minCov) {
+            st_.targets_dropped++;
+        } else {
+            if (unit_->targets() && (unit_->targets() >= o_.batchTargets || unit_->bytes + cur_bytes_ > o_.batchBytes)) flush_unit();
+            for (auto& b : cur_blocks_)
+                if (unit_->blocks.empty() || unit_->blocks.back() != b) unit_->blocks.push_back(b);
+            unit_->lines.insert(unit_->lines.end(), cur_lines_.begin(), cur_lines_.end());
+            unit_->tgt_begin.push_back((uint32_t)unit_->lines.size());
+            unit_->bytes += cur_bytes_;
+        }
+        cur_lines_.clear();
+        cur_blocks_.clear();
+        cur_bytes_ = 0;
+    }
+
+    void flush_unit() {
+        if (unit_->targets() == 0) return;
+        unit_->seq = next_seq_++;
+        out_.push(std::move(unit_));
+        unit_.reset(new WorkUnit());
+    }
+
+    const ProgramOpts& o_;
+    TextFormat fmt_;
+    Channel<std::unique_ptr<WorkUnit>>& out_;
+    RunStats& st_;
+    std::unique_ptr<WorkUnit> unit_;
+    std::string cur_id_;
+    bool have_id_ = false, blank_pending_ = false;
+    std::vector<std::pair<const char*, size_t>> cur_lines_;
+    std::vector<std::shared_ptr<Block>> cur_blocks_;
+    size_t cur_bytes_ = 0, scanned_ = 0;
+    uint64_t next_seq_ = 0;
+};
+
+// Packed batches come out of the packers in any order; the dispatcher takes them by sequence number.
+class OrderedOutbox {
+public:
+    void put(std::unique_ptr<HostBatch> b) {
+        std::lock_guard<std::mutex> lk(mu_);
+        const uint64_t s = b->seq;
+        ready_[s] = std::move(b);
+        cv_.notify_all();
+    }
+    // nullptr when the stream is finished (or failed)
+    std::unique_ptr<HostBatch> take(uint64_t seq) {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return ready_.count(seq) || done_; });
+        auto it = ready_.find(seq);
+        if (it == ready_.end()) return nullptr;
+        auto b = std::move(it->second);
+        ready_.erase(it);
+        return b;
+    }
+    void finish() {
+        std::lock_guard<std::mutex> lk(mu_);
+        done_ = true;
+        cv_.notify_all();
+    }
+
+private:
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::map<uint64_t, std::unique_ptr<HostBatch>> ready_;
+    bool done_ = false;
+};
+
+struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
+    const ProgramOpts& o;
+    TextFormat fmt;
+    bool pinned;
+    RunStats& st;
+    Channel<std::unique_ptr<WorkUnit>> units{4};
+    Channel<std::unique_ptr<HostBatch>> free_batches{1024};
+    OrderedOutbox outbox;
+    std::vector<std::thread> threads;
+    std::mutex err_mu;
+    std::string err;
+    int rc = 0;
+    int live_packers = 0;
+
+    Front(const ProgramOpts& o_, bool pinned_, RunStats& st_) : o(o_), fmt(o_.align ? TextFormat::PRE : TextFormat::M5), pinned(pinned_), st(st_) {}
+
+    void fail(int code, const std::string& msg) {
+        std::lock_guard<std::mutex> lk(err_mu);
+        if (!rc) { rc = code; err = msg; }
+    }
+
+    void start(size_t pool) {
+        for (size_t i = 0; i < pool; i++) {
+            const size_t acap = std::min<size_t>(o.batchBytes + (o.batchBytes >> 3), 8ull << 30);
+            free_batches.push(std::unique_ptr<HostBatch>(new HostBatch(pinned, acap, 64 * o.batchTargets, o.batchTargets + 1)));
+        }
+        const int np = std::max(1, o.threads);
+        live_packers = np;
+        threads.emplace_back([this] {
+            const auto t0 = std::chrono::steady_clock::now();
+            try {
+                Scanner(o, fmt, units, st).run();
+            } catch (const M5Exception::FileOpenError&) { fail(DGC_E_INVALID, "Error opening file: " + o.input);
+            } catch (const M5Exception::FormatError& e) { fail(DGC_E_INVALID, "Format error. Input: " + o.input + ", Error: " + e.msg);
+            } catch (const std::exception& e) { fail(DGC_E_INVALID, e.what()); }
+            st.scan_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            units.close();
+        });
+        for (int i = 0; i < np; i++) {
+            threads.emplace_back([this] {
+                std::unique_ptr<WorkUnit> u;
+                while (units.pop(u)) {
+                    std::unique_ptr<HostBatch> hb;
+                    if (!free_batches.pop(hb)) break;
+                    try {
+                        hb->clear();
+                        hb->seq = u->seq;
+                        std::vector<std::pair<const char*, size_t>> lines;
+                        for (size_t t = 0; t + 1 < u->tgt_begin.size(); t++) {
+                            lines.assign(u->lines.begin() + u->tgt_begin[t], u->lines.begin() + u->tgt_begin[t + 1]);
+                            hb->add_target_lines(lines, fmt);
+                        }
+                    } catch (const M5Exception::FormatError& e) { fail(DGC_E_INVALID, "Format error. Input: " + o.input + ", Error: " + e.msg);
+                    } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); }
+                    u.reset();
+                    outbox.put(std::move(hb));
+                }
+                std::lock_guard<std::mutex> lk(err_mu);
+                if (--live_packers == 0) outbox.finish();
+            });
+        }
+    }
+
+    void recycle(std::unique_ptr<HostBatch> hb) { free_batches.push(std::move(hb)); }
+
+    void stop() {
+        units.close();
+        free_batches.close();
+        for (auto& t : threads) t.join();
+        threads.clear();
+    }
+};
+
+void append_int(std::string& s, long long v) {
+    char buf[24];
+    const int n = snprintf(buf, sizeof buf, "%lld", v);
+    s.append(buf, (size_t)n);
+}
+
+}  // namespace
+
+int pack_text(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err) {
+    Front fr(opts, pinned, stats);
+    fr.start(std::max(2, opts.threads) + 1);
+    for (uint64_t seq = 0;; seq++) {
+        auto hb = fr.outbox.take(seq);
+        if (!hb) break;
+        if (!fr.rc) { sink(*hb, user); stats.batches++; }
+        fr.recycle(std::move(hb));
+    }
+    fr.stop();
+    err = fr.err;
+    return fr.rc;
+}
+
+int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (opts.align) {
+        err = "-a (re-align 'pre' records before consensus) needs the blasr SDPAlign/GuidedAlign step whose source is not "
+              "part of the reference tree; this build accepts gapped m5 input only";
+        return DGC_E_INVALID;
+    }
+    int ndev = dgc_device_count();
+    if (ndev <= 0) {
+        err = "no CUDA device: the consensus path runs on the GPU only (there is no CPU fallback)";
+        return DGC_E_NODEVICE;
+    }
+    const int G = opts.gpus > 0 ? std::min(opts.gpus, ndev) : ndev;
+    std::vector<dgc_handle*> hs((size_t)G, nullptr);
+    auto destroy_all = [&] { for (auto h : hs) if (h) dgc_destroy(h); };
+    for (int g = 0; g < G; g++) {
+        dgc_opts o{};
+        o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = g;
+        const int rc = dgc_create(&o, &hs[(size_t)g]);
+        if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); destroy_all(); return rc; }
+    }
+
+    Front fr(opts, true, stats);
+    fr.start((size_t)G * DGC_MAX_INFLIGHT + 2);
+
+    std::deque<std::unique_ptr<HostBatch>> inflight;  // in submit (= input) order; batch k runs on GPU k % G
+    std::vector<int> on_gpu((size_t)G, 0);
+    std::string text;
+    int rc = 0;
+
+    auto collect_oldest = [&]() {
+        auto hb = std::move(inflight.front());
+        inflight.pop_front();
+        const int g = (int)(hb->seq % (uint64_t)G);
+        dgc_results r{};
+        const int c = dgc_collect(hs[(size_t)g], &r);
+        on_gpu[(size_t)g]--;
+        if (c) {
+            if (!rc) { rc = c; err = std::string("dgc_collect: ") + dgc_last_error(hs[(size_t)g]); }
+        } else if (!rc) {
+            text.clear();
+            for (uint32_t t = 0; t < r.n_targets; t++) {
+                for (uint32_t f = r.tgt_frag_begin[t]; f < r.tgt_frag_begin[t + 1]; f++) {
+                    text.push_back('>');
+                    text += hb->ids[t];
+                    text.push_back('/');
+                    append_int(text, r.frag_range0[f]);
+                    text.push_back('_');
+                    append_int(text, r.frag_range1[f]);
+                    text.push_back('\n');
+                    text.append((const char*)r.seq_arena + r.frag_seq_off[f], r.frag_seq_len[f]);
+                    text.push_back('\n');
+                    stats.records++;
+                    stats.bases += r.frag_seq_len[f];
+                }
+            }
+            if (!text.empty() && fwrite(text.data(), 1, text.size(), out) != text.size()) { rc = DGC_E_INVALID; err = "write error on the FASTA output"; }
+        }
+        fr.recycle(std::move(hb));
+    };
+
+    for (uint64_t seq = 0;; seq++) {
+        auto hb = fr.outbox.take(seq);
+        if (!hb) break;
+        if (rc || fr.rc) { fr.recycle(std::move(hb)); continue; }
+        const int g = (int)(seq % (uint64_t)G);
+        while (on_gpu[(size_t)g] >= DGC_MAX_INFLIGHT) collect_oldest();
+        const dgc_batch b = hb->view();
+        // the dgc_batch struct is read during submit only; the arrays it points to stay alive in `inflight`
+        const int c = dgc_submit(hs[(size_t)g], &b);
+        if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); fr.recycle(std::move(hb)); continue; }
+        on_gpu[(size_t)g]++;
+        stats.batches++;
+        inflight.push_back(std::move(hb));
+    }
+    while (!inflight.empty()) collect_oldest();
+    fflush(out);
+    fr.stop();
+    destroy_all();
+    if (!rc && fr.rc) { rc = fr.rc; err = fr.err; }
+    stats.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return rc;
+}
+
+}  // namespace dgh

@@ -1,0 +1,113 @@
+"""GPU suite, part 2: the CUDA path and the C++ `pbdagcon` CLI against the committed golden vectors
+(tests/golden/, generated from the unmodified reference) and against oracle/_ref/pbdagcon_ref where it
+travelled to the box.  Nothing here reads /root/reference."""
+import hashlib
+import json
+import os
+import subprocess
+
+import pytest
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+EXE = os.path.join(ROOT, "pbdagcon_b200", "host", "pbdagcon")
+
+
+def md5(b):
+    return hashlib.md5(b if isinstance(b, bytes) else b.encode()).hexdigest()
+
+
+def load(name):
+    return json.load(open(os.path.join(GOLD, name)))
+
+
+def canon(text):
+    lines = text.split("\n")
+    return "".join(sorted(lines[i] + "\n" + lines[i + 1] + "\n" for i in range(0, len(lines) - 1, 2)))
+
+
+@pytest.fixture(scope="module")
+def api():
+    import __graft_entry__ as ge
+    if not os.path.exists(EXE):
+        ge.build_host()
+    import pbdagcon_b200.api as api
+    return api
+
+
+def run_cli(args, path):
+    r = subprocess.run([EXE] + args + [path], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    return r.stdout
+
+
+def test_golden_targets(api):
+    import pbdagcon_b200.synth as synth
+    cases = load("golden_targets.json")["cases"]
+    # one engine per distinct flag set, all of its cases in one batch
+    groups = {}
+    for i, c in enumerate(cases):
+        groups.setdefault((c["trim"], c["min_weight"], c["min_len"], c["backbone"] is not None), []).append(i)
+    for (trim, minw, minlen, has_bb), idx in groups.items():
+        tg = [(cases[i]["tlen"], cases[i]["backbone"].encode() if has_bb else None,
+               [(q.encode(), t.encode(), s) for q, t, s in cases[i]["alns"]]) for i in idx]
+        eng = api.Consensus(min_cov=minw, min_len=minlen, trim=trim)
+        res = eng(api.PackedBatch.from_synth(synth.from_python(tg, with_backbone=has_bb)))
+        eng.close()
+        for j, i in enumerate(idx):
+            # the pipeline's minCov filter (alns.size() < minCov) is part of the CLI path only in the golden run:
+            # min_cov == min_weight here and every case has >= 1 alignment; skipped targets yield no fragments
+            exp = cases[i]["frags"] if len(cases[i]["alns"]) >= minw else []
+            assert [[a, b, s.decode()] for a, b, s in res.frags(j)] == exp, f"case {i}"
+
+
+def test_golden_synth_workloads(api):
+    import pbdagcon_b200.synth as synth
+    for w in load("golden_synth.json")["workloads"]:
+        b = synth.gen_batch(w["seed"], w["L"], w["cov"], 0, w["targets"])
+        eng = api.Consensus(min_cov=8, min_len=500, trim=50)
+        res = eng(api.PackedBatch.from_synth(b))
+        eng.close()
+        for t in range(w["targets"]):
+            assert [[a, e, md5(s)] for a, e, s in res.frags(t)] == w["frags"][t], f"seed {w['seed']} target {t}"
+
+
+def test_cli_config1_goldens(api, tmp_path):
+    """BASELINE configs[0]: the reference's shipped m5 fixtures through the CLI, FASTA byte-identical."""
+    for name, f in load("golden_m5.json")["files"].items():
+        p = tmp_path / name
+        p.write_text("\n".join(f["lines"]) + "\n")
+        for run in f["runs"]:
+            out = run_cli(run["flags"], str(p))
+            assert out == run["fasta"] and md5(out) == run["md5"], (name, run["flags"])
+        # stdin input ("-"), as the reference accepts it (main.cpp:58-59)
+        r = subprocess.run([EXE, "-c", "1", "-m", "1", "-t", "0", "-"], input=p.read_text(), stdout=subprocess.PIPE, text=True, timeout=120)
+        assert r.returncode == 0 and r.stdout == f["runs"][0]["fasta"]
+
+
+def test_cli_synth_golden_fasta(api, tmp_path):
+    import pbdagcon_b200.synth as synth
+    for w in load("golden_synth.json")["workloads"]:
+        path = str(tmp_path / f"w{w['seed']}.m5")
+        synth.write_m5(w["seed"], w["L"], w["cov"], 0, w["targets"], path)
+        out = run_cli(["-c", "8", "-j", "3", "--batch-targets", "2"], path)
+        assert md5(canon(out)) == w["fasta_sorted_md5"]
+        ids = [ln.split("/")[1] for ln in out.split("\n") if ln.startswith(">")]
+        assert ids == sorted(ids, key=int), "records must come out in input-target order"
+
+
+@pytest.mark.skipif(not os.path.exists(helpers.REF_BIN), reason="oracle/_ref/pbdagcon_ref did not travel")
+def test_cli_matches_reference_binary(api, tmp_path):
+    """200 targets of the config-2 shape, the CLI against the reference CLI on the same m5 file."""
+    import pbdagcon_b200.synth as synth
+    path = str(tmp_path / "c2.m5")
+    synth.write_m5(2, 8000, 30, 100, 200, path)
+    ref = subprocess.run([helpers.REF_BIN, "-j", "8", "-c", "8", path], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=900)
+    assert ref.returncode == 0
+    out = run_cli(["-c", "8", "-j", "4", "--batch-targets", "64"], path)
+    assert canon(out) == canon(ref.stdout)
+    assert out.count(">") >= 200
