@@ -233,8 +233,16 @@ int launch_normalize(Slot& s, const dgc_dbatch& db) {
     na.norm = s.norm.as<u16>(); na.o_off = s.o_off.as<u64>(); na.o_len = s.o_len.as<u32>(); na.o_start = s.o_start.as<u32>();
     na.o_flags = s.o_flags.as<u32>(); na.o_nI = s.o_nI.as<u32>(); na.o_nE = s.o_nE.as<u32>(); na.o_tkept = s.o_tkept.as<u32>();
     if (db.A) {
-        k_normalize_trim<<<(db.A + 127) / 128, 128, 0, s.stream>>>(na);
-        s.tm.launches++;
+        if (o.flags & DGC_F_NO_NORMALIZE) {
+            na.retry_only = 0;
+            k_normalize_trim<<<(db.A + 127) / 128, 128, 0, s.stream>>>(na);
+            s.tm.launches++;
+        } else {
+            na.retry_only = 1;
+            k_normalize_warp<<<(db.A + NW_WARPS - 1) / NW_WARPS, NW_WARPS * 32, 0, s.stream>>>(na);
+            k_normalize_trim<<<(db.A + 127) / 128, 128, 0, s.stream>>>(na);  // the few the warp kernel handed back
+            s.tm.launches += 2;
+        }
     }
     CU(cudaGetLastError());
     return DGC_OK;

@@ -71,7 +71,8 @@ __device__ __forceinline__ u32 n_flags(u32 bfv) { return (bfv >> 8) & 0xFFu; }
 __device__ __forceinline__ u32 n_vis(u32 bfv) { return bfv >> 16; }
 
 // ------------------------------------------------------------------------------------------
-// K1: normalizeGaps + trimAln, one thread per alignment.
+// K1 (serial form): normalizeGaps + trimAln, one thread per alignment.  Runs the alignments the warp kernel
+// (normalize_warp.cuh) hands back (AF_RETRY) and everything when normalisation is switched off.
 // normalizeGaps is a left-to-right transducer with look-ahead: column i may pull the next
 // target (query) base leftwards into its gap (Alignment.cpp:167-197).  Because a pull always
 // takes the *next* non-gap character, the mutated state is fully described by two cursors
@@ -135,6 +136,7 @@ struct NormArgs {
     const u64* aln_t_off;
     const u64* aln_norm_off;  // column offset of this alignment's slot in `norm` (capacity 2*len)
     u32 n_alns, min_len, trim, flags;
+    u32 retry_only;  // serial kernel: handle only the alignments the warp kernel flagged AF_RETRY
     u16* norm;  // q | t << 8 per column
     u64* o_off;
     u32* o_len;
@@ -148,6 +150,7 @@ struct NormArgs {
 __global__ void __launch_bounds__(128) k_normalize_trim(NormArgs a) {
     u32 ai = blockIdx.x * blockDim.x + threadIdx.x;
     if (ai >= a.n_alns) return;
+    if (a.retry_only && a.o_flags[ai] != 2u /* AF_RETRY */) return;
     const u64 n = a.aln_len[ai];
     const u64 base = a.aln_norm_off[ai];
     u16* out = a.norm + base;
@@ -218,6 +221,8 @@ __global__ void __launch_bounds__(128) k_normalize_trim(NormArgs a) {
     a.o_nE[ai] = nE;
     a.o_tkept[ai] = tk;
 }
+
+#include "normalize_warp.cuh"
 
 // ------------------------------------------------------------------------------------------
 // K1b: per target, the min-coverage filter (main.cpp:66-72,118), alignment validation, and the

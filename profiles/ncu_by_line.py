@@ -22,16 +22,16 @@ def sass_lines(kernel):
         subprocess.run(["cuobjdump", "-xelf", "all", SO], cwd=d, check=True, stdout=subprocess.DEVNULL)
         cubin = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
         txt = subprocess.run(["nvdisasm", "--print-line-info", cubin], cwd=d, check=True, stdout=subprocess.PIPE, text=True).stdout
-    out, cur, infn = [], 0, False
+    out, cur, infn = [], ("?", 0), False
     for ln in txt.splitlines():
         if ln.startswith(".text."):
             infn = kernel in ln
             continue
         if not infn:
             continue
-        m = re.search(r'//## File ".*?", line (\d+)', ln)
+        m = re.search(r'//## File "(.*?)", line (\d+)', ln)
         if m:
-            cur = int(m.group(1))
+            cur = (os.path.basename(m.group(1)), int(m.group(2)))
             continue
         if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+\S", ln):
             out.append(cur)
@@ -59,14 +59,23 @@ def main():
     for ln, r in zip(lines, body):
         a = agg.setdefault(ln, [0, 0, 0, 0])
         a[0] += int(r[ci] or 0); a[1] += int(r[cs] or 0); a[2] += int(r[ct] or 0); a[3] += 1
-    src = open(os.path.join(ROOT, "pbdagcon_b200", "csrc", "dagcon_kernels.cuh")).read().splitlines()
+    srcs = {}
+
+    def text(key):
+        f, n = key
+        if f not in srcs:
+            try:
+                srcs[f] = open(os.path.join(ROOT, "pbdagcon_b200", "csrc", f)).read().splitlines()
+            except OSError:
+                srcs[f] = []
+        return srcs[f][n - 1].strip()[:100] if 0 < n <= len(srcs[f]) else ""
     ti = sum(a[0] for a in agg.values()) or 1
     ts = sum(a[1] for a in agg.values()) or 1
     print(f"{kernel}: {ti} warp instructions, {ts} stall samples, {len(body)} SASS instructions")
-    print(f"{'line':>5} {'inst%':>6} {'stall%':>6} {'thr/inst':>8} {'sass':>4}  source")
+    print(f"{'file:line':>20} {'inst%':>6} {'stall%':>6} {'thr/inst':>8} {'sass':>4}  source")
     for ln, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
-        s = src[ln - 1].strip()[:110] if 0 < ln <= len(src) else ""
-        print(f"{ln:5d} {100 * a[0] / ti:6.2f} {100 * a[1] / ts:6.2f} {a[2] / max(1, a[0]):8.1f} {a[3]:4d}  {s}")
+        s = text(ln)
+        print(f"{ln[0][:14]:>14}:{ln[1]:<5d} {100 * a[0] / ti:6.2f} {100 * a[1] / ts:6.2f} {a[2] / max(1, a[0]):8.1f} {a[3]:4d}  {s}")
 
 
 if __name__ == "__main__":
