@@ -1022,6 +1022,8 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_best_path(SerialArgs a) {
     if (status != T_OK) { a.tgt_status[t] = status; a.tgt_nfrag[t] = 0; }
 }
 
+#include "graph_v2.cuh"
+
 // ------------------------------------------------------------------------------------------
 // Output compaction: exclusive scans over targets (one block), then a gather.
 __global__ void __launch_bounds__(1024) k_scan_outputs(u32 n, const u32* status, const u32* cons_len, const u32* nfrag,
