@@ -94,11 +94,11 @@ struct Slot {
     DevBuf o_off, o_len, o_start, o_flags, o_nI, o_nE, o_tkept, norm;
     // per-target arrays
     DevBuf t_status, t_V, t_E, t_cols, t_ne, t_nv, t_cons_len, t_nfrag, t_cons_coff, t_frag_coff, totals;
-    DevBuf bb_off, ins_off, pool_off, pool_cap, t_pool_top, cons_off, frag_off, frag_cap, gs_off, gs_cap;
+    DevBuf rec_off, pos_off, pool_cap, t_pool_top, cons_off, frag_off, frag_cap, gs_off, gs_cap;
     HostBuf hp_plan_in;   // status, V, E, cols read back after the plan kernel
     HostBuf hp_plan_out;  // the offset arrays
     // chunk arenas
-    DevBuf bbrec, insrec, pool, cons, frags, gscratch, gacc;
+    DevBuf rec, cons, frags, gscratch, gacc;
     // compacted outputs
     DevBuf out_cons, out_frags;
     HostBuf r_status, r_cons_coff, r_frag_coff, r_totals, r_cons, r_frags, r_nfrag;
@@ -248,7 +248,7 @@ int launch_normalize(Slot& s, const dgc_dbatch& db) {
     return DGC_OK;
 }
 
-struct Chunk { uint32_t first, count; uint64_t nBB, nIns, nPool, nCons, nFrag, nGs; uint32_t maxL2; };
+struct Chunk { uint32_t first, count; uint64_t nUnits, nPos, nCons, nFrag, nGs; uint32_t maxL2; };
 
 // The whole hot path for a resident batch.  stop_after: 0 build, 1 merge, 2 everything.
 int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) {
@@ -269,7 +269,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     for (DevBuf* b : {&s.t_status, &s.t_V, &s.t_E, &s.t_ne, &s.t_nv, &s.t_cons_len, &s.t_nfrag, &s.frag_cap, &s.gs_cap, &s.t_frag_coff,
                       &s.pool_cap, &s.t_pool_top})
         CU(b->ensure(4 * (T + 1)));
-    for (DevBuf* b : {&s.t_cols, &s.t_cons_coff, &s.bb_off, &s.ins_off, &s.pool_off, &s.cons_off, &s.frag_off, &s.gs_off})
+    for (DevBuf* b : {&s.t_cols, &s.t_cons_coff, &s.rec_off, &s.pos_off, &s.cons_off, &s.frag_off, &s.gs_off})
         CU(b->ensure(8 * (T + 1)));
     CU(s.totals.ensure(64));
     CU(s.hp_plan_in.ensure(20 * (T + 1) + 16));
@@ -301,11 +301,10 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     CU(cudaMemcpyAsync(hp_cols, s.t_cols.p, 8 * T, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
 
-    // ---- host planning: record/pool offsets per target, chunks that fit the scratch budget
-    uint64_t* p_bb = s.hp_plan_out.as<uint64_t>();
-    uint64_t* p_ins = p_bb + (T + 1);
-    uint64_t* p_pool = p_ins + (T + 1);
-    uint64_t* p_cons = p_pool + (T + 1);
+    // ---- host planning: arena offsets per target (128-byte units), chunks that fit the scratch budget
+    uint64_t* p_rec = s.hp_plan_out.as<uint64_t>();
+    uint64_t* p_pos = p_rec + (T + 1);
+    uint64_t* p_cons = p_pos + (T + 1);
     uint64_t* p_frag = p_cons + (T + 1);
     uint64_t* p_gs = p_frag + (T + 1);
     uint32_t* p_fcap = (uint32_t*)(p_gs + (T + 1));
@@ -313,53 +312,53 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     uint32_t* p_pcap = p_gcap + (T + 1);
     uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (32ull << 30);
     std::vector<Chunk> chunks;
-    Chunk cur{0, 0, 0, 0, 0, 0, 0, 0, 0};
-    auto chunk_bytes = [](const Chunk& c) { return (256 + 9) * c.nBB + 128 * c.nIns + 8 * c.nPool + c.nCons + 8 * c.nFrag + 4 * c.nGs; };
+    Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
+    auto chunk_bytes = [](const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; };
     uint64_t out_cons_cap = 0, out_frag_cap = 0;
     for (size_t t = 0; t < T; t++) {
         const bool ok = hp_status[t] == T_OK && (only_target == 0xFFFFFFFFu || only_target == t);
         if (!ok && hp_status[t] == T_OK) hp_status[t] = T_SKIPPED;  // debug single-target run
         const uint64_t V = ok ? hp_V[t] : 0, E = ok ? hp_E[t] : 0, L2 = ok ? (uint64_t)db.h_tlen[t] + 2 : 0;
-        const uint64_t nI = V - L2;
         const uint32_t A = db.h_aln_begin[t + 1] - db.h_aln_begin[t];
-        // list blocks: enter's out-list and exit's in-list always; the rest only when a list outgrows its record
-        const uint64_t pcap = ok ? 4ull * (A + 8) + E / 2 + 256 : 0;
+        // pool of list blocks behind the records: enter's out-list and exit's in-list always, the rest only when a
+        // list outgrows its record; a multiple of 16 words keeps every target's arena 128-byte aligned
+        const uint64_t pcap = ok ? (4ull * (A + 8) + E / 2 + 256 + 15) & ~15ull : 0;
+        const uint64_t units = ok ? L2 + V + pcap / 16 : 0;  // backbone records take two units
         const uint64_t fcap = ok ? V / ((uint64_t)o.min_len + 1) + 2 : 0, gcap = ok ? 8ull * (A + 2) + 64 : 0;
         const uint64_t consb = (V + 15) & ~15ull;
-        Chunk one{0, 1, L2, nI, pcap, consb, fcap, gcap, (uint32_t)L2};
-        if (pcap > 0xFFFFFFF0ull) { s.err = "target too large"; return DGC_E_NOMEM; }
+        Chunk one{0, 1, units, L2, consb, fcap, gcap, (uint32_t)L2};
+        if (16 * units > 0xFFFFFFF0ull) { s.err = "one target's graph exceeds the 32 GiB a list pointer can address"; return DGC_E_NOMEM; }
         if (chunk_bytes(one) > budget) { s.err = "one target needs more than scratch_bytes of graph arena"; return DGC_E_NOMEM; }
         Chunk nxt = cur;
-        nxt.nBB += L2; nxt.nIns += nI; nxt.nPool += pcap; nxt.nCons += consb; nxt.nFrag += fcap; nxt.nGs += gcap; nxt.count++;
+        nxt.nUnits += units; nxt.nPos += L2; nxt.nCons += consb; nxt.nFrag += fcap; nxt.nGs += gcap; nxt.count++;
         if (cur.count && (chunk_bytes(nxt) > budget || cur.count >= (1u << 20))) {
             chunks.push_back(cur);
-            cur = Chunk{(uint32_t)t, 0, 0, 0, 0, 0, 0, 0, 0};
+            cur = Chunk{(uint32_t)t, 0, 0, 0, 0, 0, 0, 0};
         }
-        p_bb[t] = cur.nBB; p_ins[t] = cur.nIns; p_pool[t] = cur.nPool; p_cons[t] = cur.nCons; p_frag[t] = cur.nFrag; p_gs[t] = cur.nGs;
+        p_rec[t] = cur.nUnits; p_pos[t] = cur.nPos; p_cons[t] = cur.nCons; p_frag[t] = cur.nFrag; p_gs[t] = cur.nGs;
         p_fcap[t] = (uint32_t)fcap; p_gcap[t] = (uint32_t)gcap; p_pcap[t] = (uint32_t)pcap;
-        cur.nBB += L2; cur.nIns += nI; cur.nPool += pcap; cur.nCons += consb; cur.nFrag += fcap; cur.nGs += gcap; cur.count++;
+        cur.nUnits += units; cur.nPos += L2; cur.nCons += consb; cur.nFrag += fcap; cur.nGs += gcap; cur.count++;
         cur.maxL2 = std::max(cur.maxL2, (uint32_t)L2);
         out_cons_cap += V; out_frag_cap += fcap;
         s.tm.nodes += V; s.tm.norm_cols += ok ? hp_cols[t] : 0;
     }
     if (cur.count) chunks.push_back(cur);
     if (only_target != 0xFFFFFFFFu) CU(cudaMemcpyAsync(s.t_status.p, hp_status, 4 * T, cudaMemcpyHostToDevice, st));
-    uint64_t mBB = 0, mIns = 0, mPool = 0, mCons = 0, mFrag = 0, mGs = 0;
+    uint64_t mUnits = 0, mPos = 0, mCons = 0, mFrag = 0, mGs = 0;
     bool need_gacc = false;
     for (auto& c : chunks) {
-        mBB = std::max(mBB, c.nBB); mIns = std::max(mIns, c.nIns); mPool = std::max(mPool, c.nPool);
+        mUnits = std::max(mUnits, c.nUnits); mPos = std::max(mPos, c.nPos);
         mCons = std::max(mCons, c.nCons); mFrag = std::max(mFrag, c.nFrag); mGs = std::max(mGs, c.nGs);
         s.tm.arena_bytes += chunk_bytes(c);
         if (9ull * c.maxL2 > h->build_smem_max) need_gacc = true;
     }
     s.tm.chunks = (uint32_t)chunks.size();
-    CU(s.bbrec.ensure(256 * mBB + 256)); CU(s.insrec.ensure(128 * mIns + 256)); CU(s.pool.ensure(8 * mPool + 64));
+    CU(s.rec.ensure(128 * mUnits + 256));
     CU(s.cons.ensure(mCons + 64)); CU(s.frags.ensure(8 * mFrag + 64)); CU(s.gscratch.ensure(4 * mGs + 64));
-    if (need_gacc) CU(s.gacc.ensure(9 * mBB + 64));
+    if (need_gacc) CU(s.gacc.ensure(9 * mPos + 64));
     CU(s.out_cons.ensure(out_cons_cap + 64)); CU(s.out_frags.ensure(8 * out_frag_cap + 64));
-    CU(cudaMemcpyAsync(s.bb_off.p, p_bb, 8 * T, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(s.ins_off.p, p_ins, 8 * T, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(s.pool_off.p, p_pool, 8 * T, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.rec_off.p, p_rec, 8 * T, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.pos_off.p, p_pos, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.cons_off.p, p_cons, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.frag_off.p, p_frag, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.gs_off.p, p_gs, 8 * T, cudaMemcpyHostToDevice, st));
@@ -374,11 +373,11 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         Build2Args ba;
         ba.first = c.first; ba.tgt_tlen = db.tgt_tlen.as<u32>(); ba.tgt_aln_begin = db.tgt_aln_begin.as<u32>();
         ba.tgt_bb_off = db.has_bb ? db.tgt_bb_off.as<u64>() : nullptr; ba.arena = db.arena.as<u8>();
-        ba.tgt_status = s.t_status.as<u32>(); ba.bb_off = s.bb_off.as<u64>(); ba.ins_off = s.ins_off.as<u64>();
-        ba.pool_off = s.pool_off.as<u64>(); ba.pool_cap = s.pool_cap.as<u32>(); ba.acc_off = s.bb_off.as<u64>();
+        ba.tgt_status = s.t_status.as<u32>(); ba.rec_off = s.rec_off.as<u64>(); ba.tgt_V = s.t_V.as<u32>();
+        ba.pool_cap = s.pool_cap.as<u32>(); ba.acc_off = s.pos_off.as<u64>();
         ba.norm = s.norm.as<u16>(); ba.a_off = s.o_off.as<u64>(); ba.a_len = s.o_len.as<u32>();
         ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>();
-        ba.bb = s.bbrec.as<u8>(); ba.ins = s.insrec.as<u8>(); ba.pool = s.pool.as<u64>();
+        ba.rec = s.rec.as<u8>();
         ba.tgt_status_out = s.t_status.as<u32>(); ba.tgt_nv = s.t_nv.as<u32>(); ba.tgt_pool_top = s.t_pool_top.as<u32>();
         // per-position running sums: 9 B per position in shared memory when the longest backbone of the chunk fits
         ba.smem_positions = (uint32_t)std::min<uint64_t>(c.maxL2, h->build_smem_max / 9);
@@ -393,30 +392,26 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
 
         Serial2Args sa;
         sa.first = c.first; sa.count = c.count;
-        uint32_t tpw = o.targets_per_warp;
-        if (tpw == 0) { tpw = 1; while (tpw < 32 && c.count / tpw > (uint32_t)h->sm_count * 40u) tpw *= 2; }
-        if (tpw > 4) tpw = 4;  // the fast path needs 256 words of shared memory per worker
-        while (tpw & (tpw - 1)) tpw &= tpw - 1;
-        sa.tpw = tpw; sa.flags = o.flags; sa.min_weight = o.min_cov; sa.min_len = o.min_len;
+        sa.flags = o.flags; sa.min_weight = o.min_cov; sa.min_len = o.min_len;
         sa.tgt_tlen = db.tgt_tlen.as<u32>(); sa.tgt_aln_begin = db.tgt_aln_begin.as<u32>(); sa.tgt_status = s.t_status.as<u32>();
-        sa.bb_off = s.bb_off.as<u64>(); sa.ins_off = s.ins_off.as<u64>(); sa.pool_off = s.pool_off.as<u64>();
+        sa.rec_off = s.rec_off.as<u64>(); sa.tgt_V = s.t_V.as<u32>();
         sa.pool_cap = s.pool_cap.as<u32>(); sa.tgt_pool_top = s.t_pool_top.as<u32>(); sa.tgt_nv = s.t_nv.as<u32>();
-        sa.bb = s.bbrec.as<u8>(); sa.ins = s.insrec.as<u8>(); sa.pool = s.pool.as<u64>();
+        sa.rec = s.rec.as<u8>();
         sa.gscratch = s.gscratch.as<u32>(); sa.gscratch_off = s.gs_off.as<u64>(); sa.gscratch_cap = s.gs_cap.as<u32>();
         sa.cons = s.cons.as<u8>(); sa.cons_off = s.cons_off.as<u64>(); sa.frags = s.frags.as<int>(); sa.frag_off = s.frag_off.as<u64>();
         sa.frag_cap = s.frag_cap.as<u32>(); sa.tgt_cons_len = s.t_cons_len.as<u32>(); sa.tgt_nfrag = s.t_nfrag.as<u32>();
-        const uint32_t workers_per_block = (SERIAL_THREADS / 32) * tpw;
-        const uint32_t grid = (c.count + workers_per_block - 1) / workers_per_block;
+        const uint32_t warps_per_block = WARP_KERNEL_THREADS / 32;   // one warp per target
+        const uint32_t grid = (c.count + warps_per_block - 1) / warps_per_block;
         if (!(o.flags & DGC_F_NO_MERGE)) {
             span_begin(s, PH_MERGE);
-            k_merge_nodes2<<<grid, SERIAL_THREADS, 0, st>>>(sa);
+            k_merge_nodes2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
             s.tm.launches++;
             CU(cudaGetLastError());
             span_end(s);
         }
         if (stop_after < 2) continue;
         span_begin(s, PH_PATH);
-        k_best_path2<<<grid, SERIAL_THREADS, 0, st>>>(sa);
+        k_best_path2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
         s.tm.launches++;
         CU(cudaGetLastError());
         span_end(s);
@@ -603,8 +598,8 @@ int dgc_destroy(dgc_handle* h) {
         s.db.release();
         for (DevBuf* b : {&s.o_off, &s.o_len, &s.o_start, &s.o_flags, &s.o_nI, &s.o_nE, &s.o_tkept, &s.norm, &s.t_status, &s.t_V,
                           &s.t_E, &s.t_cols, &s.t_ne, &s.t_nv, &s.t_cons_len, &s.t_nfrag, &s.t_cons_coff, &s.t_frag_coff, &s.totals,
-                          &s.bb_off, &s.ins_off, &s.pool_off, &s.pool_cap, &s.t_pool_top, &s.cons_off, &s.frag_off, &s.frag_cap, &s.gs_off, &s.gs_cap,
-                          &s.bbrec, &s.insrec, &s.pool, &s.cons, &s.frags, &s.gscratch, &s.gacc, &s.out_cons, &s.out_frags})
+                          &s.rec_off, &s.pos_off, &s.pool_cap, &s.t_pool_top, &s.cons_off, &s.frag_off, &s.frag_cap, &s.gs_off, &s.gs_cap,
+                          &s.rec, &s.cons, &s.frags, &s.gscratch, &s.gacc, &s.out_cons, &s.out_frags})
             b->release();
         for (HostBuf* b : {&s.h_norm_off, &s.hp_plan_in, &s.hp_plan_out, &s.r_status, &s.r_cons_coff, &s.r_frag_coff, &s.r_totals,
                            &s.r_cons, &s.r_frags, &s.r_nfrag})
@@ -750,22 +745,14 @@ int dgc_debug_graph(dgc_handle* h, dgc_dbatch* db, uint32_t target, int stage, c
         uint32_t ptop = 0;
         cudaMemcpy(&ptop, s.t_pool_top.as<u32>() + target, 4, cudaMemcpyDeviceToHost);
         const uint32_t L = db->h_tlen[target], nbb = L + 2;
-        // single-target run: all arena offsets are 0
-        std::vector<uint8_t> BB((size_t)BB_REC * nbb), IN((size_t)INS_REC * (nv - nbb) + 16);
-        std::vector<uint64_t> PO((size_t)ptop + 1);
-        cudaMemcpy(BB.data(), s.bbrec.p, BB.size(), cudaMemcpyDeviceToHost);
-        if (nv > nbb) cudaMemcpy(IN.data(), s.insrec.p, (size_t)INS_REC * (nv - nbb), cudaMemcpyDeviceToHost);
-        cudaError_t e = cudaMemcpy(PO.data(), s.pool.p, 8 * (size_t)ptop, cudaMemcpyDeviceToHost);
+        // single-target run: the arena offset is 0; records, then the pool, ptop = first unused 8-byte word
+        std::vector<uint64_t> AR((size_t)ptop + 16);
+        cudaError_t e = cudaMemcpy(AR.data(), s.rec.p, 8 * (size_t)ptop, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return DGC_E_CUDA; }
-        auto rec = [&](uint32_t v) -> const uint8_t* { return v < nbb ? BB.data() + (size_t)BB_REC * v : IN.data() + (size_t)INS_REC * (v - nbb); };
-        auto outs = [&](uint32_t v) -> const OSlot* {
-            const Hdr* hd = (const Hdr*)rec(v);
-            return hd->ext_out ? (const OSlot*)(PO.data() + hd->ext_out + 1) : (const OSlot*)(rec(v) + 32);
-        };
-        auto ins = [&](uint32_t v) -> const uint32_t* {
-            const Hdr* hd = (const Hdr*)rec(v);
-            return hd->ext_in ? (const uint32_t*)(PO.data() + hd->ext_in + 1) : (const uint32_t*)(rec(v) + (v < nbb ? BB_IN_OFF : INS_IN_OFF));
-        };
+        const uint8_t* base = (const uint8_t*)AR.data();
+        auto rec = [&](uint32_t v) -> const uint8_t* { return base + (size_t)REC_UNIT * gv_handle(v, nbb); };
+        auto outs = [&](uint32_t v) -> const OSlot* { return (const OSlot*)(base + 8 * (size_t)((const Hdr*)rec(v))->out_ptr); };
+        auto ins = [&](uint32_t v) -> const uint32_t* { return (const uint32_t*)(base + 8 * (size_t)((const Hdr*)rec(v))->in_ptr); };
         char buf[160];
         for (uint32_t v = 0; v < nv; v++) {
             const Hdr* nd = (const Hdr*)rec(v);
@@ -775,19 +762,19 @@ int dgc_debug_graph(dgc_handle* h, dgc_dbatch* db, uint32_t target, int stage, c
             out += buf;
             const OSlot* o = outs(v);
             for (uint32_t i = 0; i < (nd->deg >> 16); i++) {
-                snprintf(buf, sizeof buf, " %u:%d:%d", o[i].dst, (int)(o[i].cv & ~VISBIT), (int)((o[i].cv & VISBIT) != 0));
+                snprintf(buf, sizeof buf, " %u:%d:%d", gv_vertex(o[i].dst, nbb), (int)(o[i].cv & ~VISBIT), (int)((o[i].cv & VISBIT) != 0));
                 out += buf;
             }
             out += " |";
             const uint32_t* in = ins(v);
             for (uint32_t i = 0; i < (nd->deg & 0xFFFFu); i++) {
-                const uint32_t sv = in[i];
+                const uint32_t sv = gv_vertex(in[i], nbb);
                 int cnt = -1, vis = -1;
                 if (sv < nv) {
                     const Hdr* hs = (const Hdr*)rec(sv);
                     const OSlot* os = outs(sv);
                     for (uint32_t k = 0; k < (hs->deg >> 16); k++)
-                        if (os[k].dst == v) { cnt = (int)(os[k].cv & ~VISBIT); vis = (int)((os[k].cv & VISBIT) != 0); break; }
+                        if (os[k].dst == gv_handle(v, nbb)) { cnt = (int)(os[k].cv & ~VISBIT); vis = (int)((os[k].cv & VISBIT) != 0); break; }
                 }
                 snprintf(buf, sizeof buf, " %u:%d:%d", sv, cnt, vis);
                 out += buf;

@@ -1022,7 +1022,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_best_path(SerialArgs a) {
     if (status != T_OK) { a.tgt_status[t] = status; a.tgt_nfrag[t] = 0; }
 }
 
-#include "graph_v2.cuh"
+#include "graph_rec.cuh"
 
 // ------------------------------------------------------------------------------------------
 // Output compaction: exclusive scans over targets (one block), then a gather.

@@ -1,0 +1,1002 @@
+// graph_rec.cuh -- the alignment graph as fat vertex records (K2 build, K3 mergeNodes, K4 bestPath/consensus).
+//
+// Reference semantics (verdurin/pbdagcon @ 3c382f2): src/cpp/AlnGraphBoost.cpp
+//   ctor :16-62, addAln :64-107, addEdge :109-127, mergeNodes :129-160, mergeInNodes :162-215,
+//   mergeOutNodes :217-267, markForReaper :269-273, consensus :285-373, bestPath :375-459.
+//
+// Layout.  A vertex IS its record; an edge lives in its source's out-slot (dst, count, visited) and is mirrored
+// by a 4-byte in-slot (src) at its target -- there is no edge array.  (u,v) identifies an edge because neither
+// addEdge nor the merges ever create a parallel edge (:114-121, :194-203, :248-257).
+// One target's graph is one arena of 128-byte units followed by a pool of 8-byte words:
+//   insertion vertex v >= L+2 (creation order)   1 unit : Hdr | 12 in-slots | 6 out-slots          handle v + (L+2)
+//   backbone vertex p (0 enter, 1..L, L+1 exit)   2 units: Hdr | 12 in-slots | 22 out-slots         handle 2p
+// A handle is the unit index, so a record's address is base + 128*handle for both kinds; slots hold handles.
+// Slots keep the adjacency-list ORDER the reference's tie-breaks depend on: append = write at [deg], order
+// preserving erase = shift down.  Hdr.out_ptr / Hdr.in_ptr give the list's position in 8-byte words from the
+// arena base: the inline slots at first, a pool block (word -1 = capacity) once a list outgrows them.
+// A vertex and its lists thus sit in one or two 128-byte lines, a warp reads a whole list with one load, and
+// the neighbours' headers with one more.
+#pragma once
+
+#define REC_UNIT 128u
+#define REC_IN_OFF 32u
+#define REC_OUT_OFF 80u
+#define REC_IN_CAP 12u
+#define INS_OUT_CAP 6u
+#define BB_OUT_CAP 22u
+#define VISBIT 0x80000000u
+
+struct __align__(16) Hdr {
+    u32 bfv;      // base | flags << 8 | visited-in-edge count << 16
+    u32 deg;      // in_deg | out_deg << 16
+    u32 out_ptr;  // 8-byte word index (from the arena base) of out-slot 0
+    u32 in_ptr;   // 8-byte word index of in-slot 0
+    int weight;
+    int cov;      // coverage of _bbMap[v] (bestPath, :407); an insertion vertex holds its bbmap here until the build folds
+    union {
+        float score;
+        int cnt;
+    };
+    u32 best;     // BFS queue link, then (bestPath) index of the best out-slot
+};
+struct OSlot {
+    u32 dst;
+    u32 cv;  // count | visited << 31
+};
+static_assert(sizeof(Hdr) == 32 && sizeof(OSlot) == 8, "record layout");
+
+__host__ __device__ __forceinline__ u32 gv_handle(u32 v, u32 nbb) { return v < nbb ? 2u * v : v + nbb; }
+__host__ __device__ __forceinline__ u32 gv_vertex(u32 h, u32 nbb) { return h < 2u * nbb ? h >> 1 : h - nbb; }
+__host__ __device__ __forceinline__ u32 gv_inline_out(u32 h) { return 16u * h + REC_OUT_OFF / 8; }
+__host__ __device__ __forceinline__ u32 gv_inline_in(u32 h) { return 16u * h + REC_IN_OFF / 8; }
+
+struct GV {           // one target's graph
+    u8* base;
+    u32 nbb;          // L + 2
+    u32 pool_top, pool_end;  // 8-byte word indices from base
+    u32 status;
+};
+
+__device__ __forceinline__ Hdr* gb_hdr(u8* base, u32 h) { return (Hdr*)(base + (size_t)h * REC_UNIT); }
+__device__ __forceinline__ OSlot* gb_out(u8* base, u32 out_ptr) { return (OSlot*)(base + (size_t)out_ptr * 8); }
+__device__ __forceinline__ u32* gb_in(u8* base, u32 in_ptr) { return (u32*)(base + (size_t)in_ptr * 8); }
+__device__ __forceinline__ Hdr* gv_hdr(const GV& g, u32 h) { return (Hdr*)(g.base + (size_t)h * REC_UNIT); }
+__device__ __forceinline__ OSlot* gv_out(const GV& g, u32 out_ptr) { return (OSlot*)(g.base + (size_t)out_ptr * 8); }
+__device__ __forceinline__ u32* gv_in(const GV& g, u32 in_ptr) { return (u32*)(g.base + (size_t)in_ptr * 8); }
+__device__ __forceinline__ u32 gv_out_cap(const GV& g, u32 h, u32 out_ptr) {
+    return out_ptr == gv_inline_out(h) ? (h < 2u * g.nbb ? BB_OUT_CAP : INS_OUT_CAP) : (u32)((const u64*)g.base)[out_ptr - 1];
+}
+__device__ __forceinline__ u32 gv_in_cap(const GV& g, u32 h, u32 in_ptr) {
+    return in_ptr == gv_inline_in(h) ? REC_IN_CAP : (u32)((const u64*)g.base)[in_ptr - 1];
+}
+// a pool block of `words` 8-byte words behind one capacity word; returns the index of its first data word or 0
+__device__ __forceinline__ u32 gv_alloc(GV& g, u32 words, u32 cap) {
+    if (g.pool_top + words + 1 > g.pool_end) { g.status = T_INTERNAL; return 0; }
+    const u32 off = g.pool_top;
+    g.pool_top += words + 1;
+    ((u64*)g.base)[off] = cap;
+    return off + 1;
+}
+
+// boost::edge(u, v, g): first match in out(u); returns the slot index or NIL
+__device__ __forceinline__ u32 gv_find_out(const OSlot* o, u32 n, u32 v) {
+#pragma unroll 1
+    for (u32 i = 0; i < n; i++)
+        if (o[i].dst == v) return i;
+    return NIL;
+}
+__device__ __forceinline__ OSlot* gv_edge_slot(const GV& g, u32 u, u32 v) {
+    const Hdr* hu = gv_hdr(g, u);
+    OSlot* o = gv_out(g, hu->out_ptr);
+    const u32 i = gv_find_out(o, hu->deg >> 16, v);
+    return i == NIL ? nullptr : o + i;
+}
+
+// boost::add_edge(u, v) with the AlnEdge properties copied (:198-203, :252-257); u's and v's headers are updated
+__device__ __noinline__ void gv_add_edge(GV& g, u32 u, u32 v, u32 count, u32 visited) {
+    Hdr* hu = gv_hdr(g, u);
+    {
+        const u32 n = hu->deg >> 16;
+        OSlot* o = gv_out(g, hu->out_ptr);
+        if (n == gv_out_cap(g, u, hu->out_ptr)) {
+            const u32 ncap = max(8u, 2u * n);
+            const u32 blk = gv_alloc(g, ncap, ncap);
+            if (!blk) return;
+            OSlot* no = gv_out(g, blk);
+#pragma unroll 1
+            for (u32 i = 0; i < n; i++) no[i] = o[i];
+            hu->out_ptr = blk;
+            o = no;
+        }
+        OSlot s;
+        s.dst = v; s.cv = count | (visited ? VISBIT : 0u);
+        o[n] = s;
+        hu->deg += 0x10000u;
+    }
+    Hdr* hv = gv_hdr(g, v);
+    {
+        const u32 n = hv->deg & 0xFFFFu;
+        u32* in = gv_in(g, hv->in_ptr);
+        if (n == gv_in_cap(g, v, hv->in_ptr)) {
+            const u32 ncap = max(16u, 2u * n);
+            const u32 blk = gv_alloc(g, ncap / 2, ncap);
+            if (!blk) return;
+            u32* ni = gv_in(g, blk);
+#pragma unroll 1
+            for (u32 i = 0; i < n; i++) ni[i] = in[i];
+            hv->in_ptr = blk;
+            in = ni;
+        }
+        in[n] = u;
+        hv->deg += 1u;
+        if (visited) hv->bfv += 0x10000u;
+    }
+}
+
+// order-preserving erase of the edge (u -> v) from v's in-list / u's out-list (half of boost::clear_vertex)
+__device__ __forceinline__ void gv_erase_in(GV& g, u32 v, u32 u, bool was_visited) {
+    Hdr* hv = gv_hdr(g, v);
+    const u32 n = hv->deg & 0xFFFFu;
+    u32* in = gv_in(g, hv->in_ptr);
+    u32 i = 0;
+#pragma unroll 1
+    while (i < n && in[i] != u) i++;
+    if (i == n) { g.status = T_INTERNAL; return; }
+#pragma unroll 1
+    for (; i + 1 < n; i++) in[i] = in[i + 1];
+    hv->deg -= 1u;
+    if (was_visited) hv->bfv -= 0x10000u;
+}
+__device__ __forceinline__ void gv_erase_out(GV& g, u32 u, u32 v) {
+    Hdr* hu = gv_hdr(g, u);
+    const u32 n = hu->deg >> 16;
+    OSlot* o = gv_out(g, hu->out_ptr);
+    u32 i = gv_find_out(o, n, v);
+    if (i == NIL) { g.status = T_INTERNAL; return; }
+#pragma unroll 1
+    for (; i + 1 < n; i++) o[i] = o[i + 1];
+    hu->deg -= 0x10000u;
+}
+
+// markForReaper (:269-273): deleted = true; clear_vertex(n)
+__device__ __noinline__ void gv_reap(GV& g, u32 ni) {
+    Hdr* h = gv_hdr(g, ni);
+    const u32 deg = h->deg;
+    const OSlot* o = gv_out(g, h->out_ptr);
+#pragma unroll 1
+    for (u32 i = 0; i < (deg >> 16); i++) {
+        const OSlot s = o[i];
+        if (s.dst != ni) gv_erase_in(g, s.dst, ni, (s.cv & VISBIT) != 0);
+    }
+    const u32* in = gv_in(g, h->in_ptr);
+#pragma unroll 1
+    for (u32 i = 0; i < (deg & 0xFFFFu); i++) {
+        const u32 s = in[i];
+        if (s != ni) gv_erase_out(g, s, ni);
+    }
+    h->deg = 0;
+    h->bfv = (h->bfv & 0xFFFFu) | (NF_DELETED << 8);
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: graph construction (ctor :16-62, addAln :64-107, addEdge :109-127), one 256-thread block per target.
+// Alignments are replayed in input order (every adjacency list is ordered by the alignment that first created
+// each edge); inside one alignment every vertex is entered and left at most once, so its columns are processed in
+// parallel, 1024 per tile: block scans give each column its backbone position, its insertion-vertex id and its
+// predecessor on the path.  Per backbone position the running sums (coverage, match weight, count of the ctor
+// edge p->p+1, last target base, list lengths) stay in shared memory for the whole replay and are folded into
+// the records once at the end; insertion records are written exactly once.
+struct Build2Args {
+    u32 first;
+    const u32* tgt_tlen;
+    const u32* tgt_aln_begin;
+    const u64* tgt_bb_off;  // or nullptr
+    const u8* arena;
+    const u32* tgt_status;
+    const u64* rec_off;   // first 128-byte unit of the target's arena
+    const u32* tgt_V;     // planned vertex count: the pool starts behind (L+2) + V units
+    const u32* pool_cap;  // 8-byte words
+    const u64* acc_off;   // positions before this target (global accumulator fallback)
+    const u16* norm;
+    const u64* a_off;
+    const u32* a_len;
+    const u32* a_start;
+    const u32* a_flags;
+    u8* rec;
+    u32* tgt_status_out;
+    u32* tgt_nv;
+    u32* tgt_pool_top;
+    u32 smem_positions;
+    u8* gacc;  // 9 bytes per position
+};
+
+struct BuildAcc {  // per-position running state of the replay
+    u16* cov;
+    u16* w;
+    u16* c;
+    u8* b;
+    u8* dout;
+    u8* din;
+};
+
+struct B2Ctx {
+    u8* base;
+    u32 L, A, nbb, enter_out, exit_in, pool_end;  // enter_out / exit_in: word index of slot 0 of the two wide lists
+    u32* s_pool_top;
+    u32* s_status;
+    u32* s_enter_out;
+    u32* s_exit_in;
+    BuildAcc acc;
+};
+__device__ __forceinline__ Hdr* b2_hdr(const B2Ctx& c, u32 h) { return (Hdr*)(c.base + (size_t)h * REC_UNIT); }
+
+// append (p -> dst handle, count 1) to backbone vertex p's out-list
+__device__ __forceinline__ void b2_append_out(const B2Ctx& c, u32 p, u32 dsth) {
+    u32 n, ptr;
+    if (p == 0) {
+        n = (*c.s_enter_out)++;
+        ptr = c.enter_out;
+    } else {
+        n = c.acc.dout[p];
+        if (n >= 254u) { *c.s_status = T_TOO_MANY; return; }
+        c.acc.dout[p] = (u8)(n + 1);
+        ptr = n <= BB_OUT_CAP ? gv_inline_out(2 * p) : b2_hdr(c, 2 * p)->out_ptr;
+        if (n == BB_OUT_CAP) {  // the inline slots are full: the list moves into a pool block that can hold any degree
+            const u32 cap = c.A + 2, blk = atomicAdd(c.s_pool_top, cap + 1);
+            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_INTERNAL; return; }
+            ((u64*)c.base)[blk] = cap;
+            const OSlot* o = (const OSlot*)(c.base + (size_t)ptr * 8);
+            OSlot* no = (OSlot*)(c.base + (size_t)(blk + 1) * 8);
+            for (u32 i = 0; i < n; i++) no[i] = o[i];
+            b2_hdr(c, 2 * p)->out_ptr = blk + 1;
+            ptr = blk + 1;
+        }
+    }
+    OSlot s;
+    s.dst = dsth; s.cv = 1;
+    ((OSlot*)(c.base + (size_t)ptr * 8))[n] = s;
+}
+__device__ __forceinline__ void b2_append_in(const B2Ctx& c, u32 p, u32 srch) {
+    u32 n, ptr;
+    if (p == c.L + 1) {
+        n = (*c.s_exit_in)++;
+        ptr = c.exit_in;
+    } else {
+        n = c.acc.din[p];
+        if (n >= 254u) { *c.s_status = T_TOO_MANY; return; }
+        c.acc.din[p] = (u8)(n + 1);
+        ptr = n <= REC_IN_CAP ? gv_inline_in(2 * p) : b2_hdr(c, 2 * p)->in_ptr;
+        if (n == REC_IN_CAP) {
+            const u32 cap = c.A + 2, words = (cap + 1) / 2, blk = atomicAdd(c.s_pool_top, words + 1);
+            if (blk + words + 1 > c.pool_end) { *c.s_status = T_INTERNAL; return; }
+            ((u64*)c.base)[blk] = cap;
+            const u32* in = (const u32*)(c.base + (size_t)ptr * 8);
+            u32* ni = (u32*)(c.base + (size_t)(blk + 1) * 8);
+            for (u32 i = 0; i < n; i++) ni[i] = in[i];
+            b2_hdr(c, 2 * p)->in_ptr = blk + 1;
+            ptr = blk + 1;
+        }
+    }
+    ((u32*)(c.base + (size_t)ptr * 8))[n] = srch;
+}
+
+// addEdge(prev, cur) (:109-127) for one path step; prev/cur are vertex ids.  An insertion vertex on the path was
+// created by the alignment being replayed: its single in-slot / out-slot is written directly.
+__device__ __forceinline__ void b2_edge(const B2Ctx& c, u32 prev, u32 cur) {
+    const u32 nbb = c.nbb;
+    const bool prev_bb = prev < nbb, cur_bb = cur < nbb;
+    const u32 ph = gv_handle(prev, nbb), ch = gv_handle(cur, nbb);
+    if (prev_bb && cur_bb) {
+        if (cur == prev + 1) { c.acc.c[prev]++; return; }  // the ctor edge p -> p+1
+        // a backbone->backbone skip (deletion run, alignment start or end): it may exist already
+        const u32 n = prev == 0 ? *c.s_enter_out : c.acc.dout[prev];
+        const u32 ptr = prev == 0 ? c.enter_out : (n <= BB_OUT_CAP ? gv_inline_out(ph) : b2_hdr(c, ph)->out_ptr);
+        OSlot* o = (OSlot*)(c.base + (size_t)ptr * 8);
+        for (u32 i = 0; i < n; i++)
+            if (o[i].dst == ch) { o[i].cv++; return; }
+        b2_append_out(c, prev, ch);
+        b2_append_in(c, cur, ph);
+        return;
+    }
+    if (prev_bb) b2_append_out(c, prev, ch);
+    else { OSlot s; s.dst = ch; s.cv = 1; *(OSlot*)(c.base + (size_t)ph * REC_UNIT + REC_OUT_OFF) = s; }
+    if (cur_bb) b2_append_in(c, cur, ph);
+    else *(u32*)(c.base + (size_t)ch * REC_UNIT + REC_IN_OFF) = ph;
+}
+
+__global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
+    const u32 t = a.first + blockIdx.x;
+    if (a.tgt_status[t] != T_OK) return;
+    const u32 tid = threadIdx.x;
+    const u32 L = a.tgt_tlen[t];
+    const u32 ENTER = 0, EXIT = L + 1, nbb = L + 2;
+    const u32 a0 = a.tgt_aln_begin[t], a1 = a.tgt_aln_begin[t + 1];
+    __shared__ u32 sa[BT / 32], sb[BT / 32], s_cur[TILE];
+    __shared__ u32 s_carry_t, s_carry_i, s_last, s_ins, s_pool_top, s_status, s_enter_out, s_exit_in;
+    extern __shared__ __align__(16) u8 s_dyn[];
+    u8* accbase = (nbb <= a.smem_positions) ? s_dyn : a.gacc + 9ull * a.acc_off[t];
+    B2Ctx c;
+    c.acc.cov = (u16*)accbase;
+    c.acc.w = c.acc.cov + nbb;
+    c.acc.c = c.acc.w + nbb;
+    c.acc.b = (u8*)(c.acc.c + nbb);
+    c.acc.dout = c.acc.b + nbb;
+    c.acc.din = c.acc.dout + nbb;
+    c.base = a.rec + (size_t)REC_UNIT * a.rec_off[t];
+    c.L = L; c.A = a1 - a0; c.nbb = nbb;
+    const u32 pool_begin = 16u * (nbb + a.tgt_V[t]);
+    c.pool_end = pool_begin + a.pool_cap[t];
+    c.enter_out = pool_begin + 1;                          // [cap][A+2 out-slots]
+    c.exit_in = pool_begin + 1 + (c.A + 2) + 1;            // [cap][(A+2) in-slots]
+    c.s_pool_top = &s_pool_top; c.s_status = &s_status; c.s_enter_out = &s_enter_out; c.s_exit_in = &s_exit_in;
+
+    // ctor: AlnGraphBoost(size_t) :41-62 / AlnGraphBoost(const std::string&) :16-39
+    for (u32 p = tid; p < nbb; p += BT) {
+        c.acc.cov[p] = 0; c.acc.w[p] = 0; c.acc.c[p] = 0; c.acc.b[p] = 0;
+        c.acc.dout[p] = p <= L ? 1 : 0;
+        c.acc.din[p] = p >= 1 ? 1 : 0;
+        u8* r = c.base + (size_t)REC_UNIT * 2 * p;
+        Hdr h;
+        h.bfv = 0; h.deg = 0;
+        h.out_ptr = p == ENTER ? c.enter_out : gv_inline_out(2 * p);
+        h.in_ptr = p == EXIT ? c.exit_in : gv_inline_in(2 * p);
+        h.weight = 0; h.cov = 0; h.cnt = 0; h.best = NIL;
+        *(Hdr*)r = h;
+        if (p >= 1 && p <= L) {
+            OSlot s; s.dst = 2 * (p + 1); s.cv = 0;
+            *(OSlot*)(r + REC_OUT_OFF) = s;
+            *(u32*)(r + REC_IN_OFF) = 2 * (p - 1);
+        }
+    }
+    if (tid == 0) {
+        s_ins = nbb; s_status = T_OK;
+        s_enter_out = 1; s_exit_in = 1;
+        s_pool_top = c.exit_in + (c.A + 2 + 1) / 2;
+        if (s_pool_top > c.pool_end) s_status = T_INTERNAL;
+        else {
+            ((u64*)c.base)[c.enter_out - 1] = c.A + 2;
+            ((u64*)c.base)[c.exit_in - 1] = c.A + 2;
+            OSlot s; s.dst = 2; s.cv = 0;                              // enter -> 1 (-> exit when L == 0)
+            *(OSlot*)(c.base + (size_t)c.enter_out * 8) = s;
+            *(u32*)(c.base + (size_t)c.exit_in * 8) = 2 * L;            // L -> exit
+        }
+    }
+    __syncthreads();
+    if (s_status != T_OK) { if (tid == 0) a.tgt_status_out[t] = s_status; return; }
+
+    for (u32 k = a0; k < a1; k++) {
+        if (a.a_flags[k] & AF_SKIP) continue;
+        const u32 n = a.a_len[k], start = a.a_start[k];
+        const u16* cols = a.norm + a.a_off[k];
+        if (tid == 0) { s_carry_t = 0; s_carry_i = 0; s_last = ENTER; }
+        __syncthreads();
+        for (u32 c0 = 0; c0 < n; c0 += TILE) {
+            const u32 cb = c0 + tid * CPT;
+            u32 q[CPT], tc[CPT], kind[CPT];  // kind: 0 none, 1 match, 2 deletion, 3 insertion
+            u32 nadv = 0, nins = 0, lastp = 0;
+#pragma unroll
+            for (int j = 0; j < CPT; j++) {
+                kind[j] = 0; q[j] = 0; tc[j] = 0;
+                if (cb + j < n) {
+                    const u32 col = cols[cb + j];
+                    q[j] = col & 0xFFu; tc[j] = col >> 8;
+                    // column classes exactly as addAln tests them (:75, :84, :93)
+                    if (q[j] == tc[j]) kind[j] = 1;
+                    else if (q[j] == DASH) kind[j] = 2;
+                    else if (tc[j] == DASH) kind[j] = 3;
+                }
+                if (kind[j] == 1 || kind[j] == 2) nadv++;
+                if (kind[j] == 3) nins++;
+                if (kind[j] == 1 || kind[j] == 3) lastp = tid * CPT + j + 1;
+            }
+            u32 ex_s, ex_m, tot_s, tot_m;
+            block_scan2(nadv | (nins << 16), lastp, ex_s, ex_m, tot_s, tot_m, sa, sb);
+            u32 bbpos[CPT], cur[CPT];
+            {
+                u32 tb = start + s_carry_t + (ex_s & 0xFFFFu), ib = s_ins + s_carry_i + (ex_s >> 16);
+#pragma unroll
+                for (int j = 0; j < CPT; j++) {
+                    bbpos[j] = tb;
+                    cur[j] = kind[j] == 1 ? tb : (kind[j] == 3 ? ib : NIL);
+                    if (kind[j] == 1 || kind[j] == 2) tb++;
+                    if (kind[j] == 3) ib++;
+                    s_cur[tid * CPT + j] = cur[j];
+                }
+            }
+            __syncthreads();
+            u32 prev = ex_m ? s_cur[ex_m - 1] : s_last;
+#pragma unroll
+            for (int j = 0; j < CPT; j++) {
+                const u32 p = bbpos[j];
+                if (kind[j] == 1 || kind[j] == 2) {
+                    c.acc.cov[p]++;                 // _g[_bbMap[curr]].coverage++
+                    c.acc.b[p] = (u8)tc[j];         // .base = targetBase (the last alignment in order wins)
+                    if (kind[j] == 1) c.acc.w[p]++;
+                } else if (kind[j] == 3) {
+                    const u32 hh = cur[j] + nbb;
+                    Hdr h;
+                    h.bfv = q[j]; h.deg = 0x10001u; h.out_ptr = gv_inline_out(hh); h.in_ptr = gv_inline_in(hh);
+                    h.weight = 1; h.cov = (int)p; h.cnt = 0; h.best = NIL;
+                    *b2_hdr(c, hh) = h;
+                }
+                if (kind[j] == 1 || kind[j] == 3) {
+                    b2_edge(c, prev, cur[j]);
+                    prev = cur[j];
+                }
+            }
+            __syncthreads();
+            if (tid == 0) {
+                s_carry_t += tot_s & 0xFFFFu;
+                s_carry_i += tot_s >> 16;
+                if (tot_m) s_last = s_cur[tot_m - 1];
+            }
+            __syncthreads();
+        }
+        if (tid == 0) {  // addEdge(prevVtx, _exitVtx) :106
+            b2_edge(c, s_last, EXIT);
+            s_ins += s_carry_i;
+        }
+        __syncthreads();
+    }
+    // fold the running sums into the backbone headers, then give every insertion vertex the coverage of the
+    // backbone vertex it maps to (bestPath reads _g[_bbMap[v]].coverage, :407)
+    const u8* bbstr = a.tgt_bb_off ? a.arena + a.tgt_bb_off[t] : nullptr;
+    for (u32 p = tid; p < nbb; p += BT) {
+        Hdr* hp = b2_hdr(c, 2 * p);
+        Hdr h = *hp;
+        const u32 cv = c.acc.cov[p];
+        u32 b = p == ENTER ? (u32)'^' : p == EXIT ? (u32)'$' : (bbstr ? (u32)bbstr[p - 1] : (u32)'N');
+        if (cv) b = c.acc.b[p];
+        const bool inner = p >= 1 && p <= L;
+        h.bfv = b | (NF_BACKBONE << 8);
+        const u32 dout = p == ENTER ? s_enter_out : c.acc.dout[p], din = p == EXIT ? s_exit_in : c.acc.din[p];
+        h.deg = din | (dout << 16);
+        h.weight = (inner ? 1 : 0) + (int)c.acc.w[p];
+        h.cov = (int)cv;
+        *hp = h;
+        if (p <= L) ((OSlot*)(c.base + (size_t)h.out_ptr * 8))[0].cv = c.acc.c[p];
+    }
+    const u32 nv = s_ins;
+    for (u32 v = nbb + tid; v < nv; v += BT) {
+        Hdr* hv = b2_hdr(c, v + nbb);
+        const u32 bm = (u32)hv->cov;
+        hv->cov = bm < nbb ? (int)c.acc.cov[bm] : 0;
+    }
+    if (tid == 0) {
+        a.tgt_nv[t] = nv;
+        a.tgt_pool_top[t] = s_pool_top;
+        if (s_status != T_OK) a.tgt_status_out[t] = s_status;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: mergeNodes (:129-160) -- the order-sensitive part, one WARP per target.  The breadth-first sweep itself is
+// warp-parallel: lane j holds out-slot j (or in-slot j) of the popped vertex and loads its neighbour's header, so
+// candidate detection (match_any on the base), visited marking and the in-order queue appends are a handful of
+// warp instructions regardless of the degree.  The merges themselves mutate several lists in an order-sensitive
+// way; they run on lane 0 with the scalar list primitives above.
+struct Serial2Args {
+    u32 first, count;
+    u32 flags, min_weight, min_len;
+    const u32* tgt_tlen;
+    const u32* tgt_aln_begin;
+    u32* tgt_status;
+    const u64* rec_off;
+    const u32* tgt_V;
+    const u32* pool_cap;
+    u32* tgt_pool_top;
+    const u32* tgt_nv;
+    u8* rec;
+    u32* gscratch;          // the group snapshot stack of mergeInNodes
+    const u64* gscratch_off;
+    const u32* gscratch_cap;
+    u8* cons;
+    const u64* cons_off;
+    int* frags;
+    const u64* frag_off;
+    const u32* frag_cap;
+    u32* tgt_cons_len;
+    u32* tgt_nfrag;
+};
+
+struct T2Ctx {
+    GV g;
+    u32* S;
+    u32 scap;
+};
+__device__ __forceinline__ u32 S2_get(const T2Ctx& c, u32 i) { return c.S[i]; }
+__device__ __forceinline__ bool S2_put(T2Ctx& c, u32 i, u32 v) {
+    if (i < c.scap) { c.S[i] = v; return true; }
+    c.g.status = T_INTERNAL;
+    return false;
+}
+
+// Snapshot of the merge candidates of n, in list order (the std::map<char, std::vector<VtxDesc>> built at
+// :167-181).  Frame: [n, cnt, last key + 129, parent frame, members...].
+__device__ __forceinline__ u32 m2_push_in_frame(T2Ctx& c, u32 n, u32& top, u32 parent) {
+    const Hdr* h = gv_hdr(c.g, n);
+    const u32 nin = h->deg & 0xFFFFu;
+    if (nin < 2) return NIL;
+    const u32* in = gv_in(c.g, h->in_ptr);
+    u32 cnt = 0;
+#pragma unroll 1
+    for (u32 i = 0; i < nin; i++) {
+        const u32 s = in[i];
+        if ((gv_hdr(c.g, s)->deg >> 16) == 1) { if (!S2_put(c, top + 4 + cnt, s)) return NIL; cnt++; }
+    }
+    if (cnt < 2) return NIL;
+    const u32 fb = top;
+    S2_put(c, fb, n); S2_put(c, fb + 1, cnt); S2_put(c, fb + 2, 0); S2_put(c, fb + 3, parent);
+    top += 4 + cnt;
+    return fb;
+}
+
+// next key in ascending (signed) char order; false when the map is exhausted
+__device__ __forceinline__ bool m2_next_group(T2Ctx& c, u32 fb, u32& an, u32& members) {
+    const u32 cnt = S2_get(c, fb + 1);
+    const int last = (int)S2_get(c, fb + 2) - 129;
+    int key = 1000;
+#pragma unroll 1
+    for (u32 i = 0; i < cnt; i++) {
+        const int b = (int)(signed char)n_base(gv_hdr(c.g, S2_get(c, fb + 4 + i))->bfv);
+        if (b > last && b < key) key = b;
+    }
+    if (key == 1000) return false;
+    S2_put(c, fb + 2, (u32)(key + 129));
+    an = NIL; members = 0;
+#pragma unroll 1
+    for (u32 i = 0; i < cnt; i++) {
+        const u32 ni = S2_get(c, fb + 4 + i);
+        if ((int)(signed char)n_base(gv_hdr(c.g, ni)->bfv) == key) { if (an == NIL) an = ni; members++; }
+    }
+    return true;
+}
+
+// mergeInNodes :162-215 (the recursion :212 runs on the snapshot stack)
+__device__ __noinline__ void m2_merge_in(T2Ctx& c, u32 n0) {
+    GV& g = c.g;
+    u32 top = 0;
+    u32 fb = m2_push_in_frame(c, n0, top, NIL);
+    while (fb != NIL && g.status == T_OK) {
+        u32 an, members;
+        if (!m2_next_group(c, fb, an, members)) { top = fb; fb = S2_get(c, fb + 3); continue; }
+        if (members < 2) continue;
+        const u32 cnt = S2_get(c, fb + 1);
+        const int key = (int)S2_get(c, fb + 2) - 129;
+        Hdr* han = gv_hdr(g, an);
+        if ((han->deg >> 16) == 0) { g.status = T_INTERNAL; return; }
+        OSlot* an_out = gv_out(g, han->out_ptr);  // *anoi, taken once (:186-188)
+#pragma unroll 1
+        for (u32 i = 0; i < cnt; i++) {
+            const u32 ni = S2_get(c, fb + 4 + i);
+            const Hdr* hni = gv_hdr(g, ni);
+            if (ni == an || (int)(signed char)n_base(hni->bfv) != key) continue;
+            if ((hni->deg >> 16) == 0) { g.status = T_INTERNAL; return; }
+            an_out->cv += gv_out(g, hni->out_ptr)->cv & ~VISBIT;
+            han->weight += hni->weight;
+        }
+#pragma unroll 1
+        for (u32 i = 0; i < cnt; i++) {
+            const u32 ni = S2_get(c, fb + 4 + i);
+            const Hdr* hni = gv_hdr(g, ni);
+            if (ni == an || (int)(signed char)n_base(hni->bfv) != key) continue;
+            const u32 nin = hni->deg & 0xFFFFu;
+#pragma unroll 1
+            for (u32 k = 0; k < nin; k++) {
+                // the in-list of ni is stable here: edges are only added towards `an`
+                const u32 n1 = gv_in(g, hni->in_ptr)[k];
+                Hdr* h1 = gv_hdr(g, n1);
+                OSlot* o1 = gv_out(g, h1->out_ptr);
+                const u32 d1 = h1->deg >> 16;
+                const u32 e_ni = gv_find_out(o1, d1, ni);
+                if (e_ni == NIL) { g.status = T_INTERNAL; return; }
+                const u32 cvn = o1[e_ni].cv;
+                const u32 e_an = gv_find_out(o1, d1, an);
+                if (e_an != NIL) o1[e_an].cv += cvn & ~VISBIT;
+                else gv_add_edge(g, n1, an, cvn & ~VISBIT, cvn & VISBIT);
+            }
+            gv_reap(g, ni);
+        }
+        const u32 nfb = m2_push_in_frame(c, an, top, fb);  // mergeInNodes(an) :212
+        if (nfb != NIL) fb = nfb;
+    }
+}
+
+// mergeOutNodes :217-267 for one std::map key: `an` is the first member, `others` the rest of the group in list order
+__device__ __noinline__ void m2_merge_out_member(GV& g, u32 an, u32 ni) {
+    Hdr* han = gv_hdr(g, an);
+    Hdr* hni = gv_hdr(g, ni);
+    // _g[*anii].count += _g[*ii].count (:241): the first in-edge of each; an edge's count lives in its source's slot
+    if ((han->deg & 0xFFFFu) == 0 || (hni->deg & 0xFFFFu) == 0) { g.status = T_INTERNAL; return; }
+    OSlot* ea = gv_edge_slot(g, gv_in(g, han->in_ptr)[0], an);
+    OSlot* ei = gv_edge_slot(g, gv_in(g, hni->in_ptr)[0], ni);
+    if (!ea || !ei) { g.status = T_INTERNAL; return; }
+    ea->cv += ei->cv & ~VISBIT;
+    han->weight += hni->weight;
+    const u32 nout = hni->deg >> 16;
+#pragma unroll 1
+    for (u32 k = 0; k < nout; k++) {
+        const OSlot s = gv_out(g, hni->out_ptr)[k];
+        OSlot* oa = gv_out(g, han->out_ptr);
+        const u32 e = gv_find_out(oa, han->deg >> 16, s.dst);
+        if (e != NIL) oa[e].cv += s.cv & ~VISBIT;
+        else gv_add_edge(g, an, s.dst, s.cv & ~VISBIT, s.cv & VISBIT);
+    }
+    gv_reap(g, ni);
+}
+
+// generic mergeOutNodes (:217-267) for vertices with more than 32 out-edges (enter): snapshot on the stack
+__device__ __noinline__ void m2_merge_out_generic(T2Ctx& c, u32 n) {
+    GV& g = c.g;
+    const Hdr* hn = gv_hdr(g, n);
+    const u32 nout = hn->deg >> 16;
+    if (nout < 2) return;
+    u32 cnt = 0;
+#pragma unroll 1
+    for (u32 i = 0; i < nout; i++) {
+        const u32 d = gv_out(g, hn->out_ptr)[i].dst;
+        if ((gv_hdr(g, d)->deg & 0xFFFFu) == 1) { if (!S2_put(c, 4 + cnt, d)) return; cnt++; }
+    }
+    if (cnt < 2) return;
+    S2_put(c, 0, n); S2_put(c, 1, cnt); S2_put(c, 2, 0); S2_put(c, 3, NIL);
+    u32 an, members;
+    while (g.status == T_OK && m2_next_group(c, 0, an, members)) {
+        if (members < 2) continue;
+        const int key = (int)S2_get(c, 2) - 129;
+#pragma unroll 1
+        for (u32 i = 0; i < cnt && g.status == T_OK; i++) {
+            const u32 ni = S2_get(c, 4 + i);
+            if (ni == an || (int)(signed char)n_base(gv_hdr(g, ni)->bfv) != key) continue;
+            m2_merge_out_member(g, an, ni);
+        }
+    }
+}
+
+#define FULLMASK 0xFFFFFFFFu
+// Appends the vertices `v` of the lanes in `ready` (in lane order) to the intrusive FIFO (Hdr.best links).
+__device__ __forceinline__ void m2_queue_append(const GV& g, u32 ready, bool mine, u32 v, u32& tail, u32 lane) {
+    if (!ready) return;
+    const u32 before = ready & ((1u << lane) - 1u);
+    const u32 src = before ? 31u - (u32)__clz((int)before) : 0u;
+    const u32 pv = __shfl_sync(FULLMASK, v, src);
+    if (mine) gv_hdr(g, before ? pv : tail)->best = v;
+    tail = __shfl_sync(FULLMASK, v, 31u - (u32)__clz((int)ready));
+}
+
+__device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx& c) {
+    const u32 idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (idx >= a.count) return false;
+    t = a.first + idx;
+    if (a.tgt_status[t] != T_OK) return false;
+    c.g.base = a.rec + (size_t)REC_UNIT * a.rec_off[t];
+    c.g.nbb = a.tgt_tlen[t] + 2;
+    const u32 pool_begin = 16u * (c.g.nbb + a.tgt_V[t]);
+    c.g.pool_top = a.tgt_pool_top[t];
+    c.g.pool_end = pool_begin + a.pool_cap[t];
+    c.g.status = T_OK;
+    c.S = a.gscratch + a.gscratch_off[t];
+    c.scap = a.gscratch_cap[t];
+    return true;
+}
+
+#define WARP_KERNEL_THREADS 128
+
+// mergeNodes :129-160
+__global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_merge_nodes2(Serial2Args a) {
+    u32 t;
+    T2Ctx c;
+    if (!warp2_setup(a, t, c)) return;
+    GV& g = c.g;
+    const u32 lane = threadIdx.x & 31;
+    const u32 ENTER = 0;
+    u32 head = ENTER, tail = ENTER, status = T_OK;
+    if (lane == 0) { gv_hdr(g, ENTER)->best = NIL; gv_hdr(g, ENTER)->bfv |= NF_QUEUED << 8; }
+    __syncwarp();
+    while (head != NIL && status == T_OK) {
+        const u32 u = head;
+        Hdr* pu = gv_hdr(g, u);
+        Hdr hu = *pu;
+        // ---- mergeInNodes(u): is there a group of >= 2 predecessors with out_degree 1 and the same base?
+        u32 nin = hu.deg & 0xFFFFu;
+        if (nin >= 2) {
+            bool need = nin > 32;  // only exit gets that wide: let the scalar code decide
+            if (!need) {
+                const bool have = lane < nin;
+                const u32 s = have ? gv_in(g, hu.in_ptr)[lane] : 0u;
+                uint2 d = make_uint2(0u, 0u);
+                if (have) d = *(const uint2*)gv_hdr(g, s);
+                const bool cand = have && (d.y >> 16) == 1;
+                const u32 grp = __match_any_sync(FULLMASK, cand ? (d.x & 0xFFu) : 0x100u + lane);
+                need = cand && __popc(grp) > 1;
+            }
+            if (__any_sync(FULLMASK, need)) {
+                if (lane == 0) m2_merge_in(c, u);
+                __syncwarp();
+                status = __shfl_sync(FULLMASK, g.status, 0);
+                hu = *pu;
+            }
+        }
+        // ---- mergeOutNodes(u), then mark the out-edges visited and enqueue the successors that became ready
+        u32 nout = hu.deg >> 16;
+        if (nout > 32) {  // enter (one edge per alignment start): scalar
+            if (lane == 0) {
+                m2_merge_out_generic(c, u);
+                hu = *pu;
+                nout = hu.deg >> 16;
+#pragma unroll 1
+                for (u32 i = 0; i < nout && g.status == T_OK; i++) {
+                    OSlot* o = gv_out(g, hu.out_ptr) + i;
+                    Hdr* hv = gv_hdr(g, o->dst);
+                    if (!(o->cv & VISBIT)) { o->cv |= VISBIT; hv->bfv += 0x10000u; }
+                    const u32 bfv = hv->bfv;
+                    if (n_vis(bfv) == (hv->deg & 0xFFFFu)) {  // notVisited == 0
+                        if (n_flags(bfv) & NF_QUEUED) { g.status = T_INTERNAL; break; }
+                        hv->bfv = bfv | (NF_QUEUED << 8);
+                        gv_hdr(g, tail)->best = o->dst;
+                        tail = o->dst;
+                    }
+                }
+            }
+            __syncwarp();
+            tail = __shfl_sync(FULLMASK, tail, 0);
+            status = __shfl_sync(FULLMASK, g.status, 0);
+            head = pu->best;
+            continue;
+        }
+        bool have = lane < nout;
+        OSlot sl;
+        sl.dst = 0; sl.cv = 0;
+        uint2 d = make_uint2(0u, 0u);
+        if (have) { sl = gv_out(g, hu.out_ptr)[lane]; d = *(const uint2*)gv_hdr(g, sl.dst); }
+        {
+            const bool cand = have && (d.y & 0xFFFFu) == 1;
+            const u32 key = d.x & 0xFFu;
+            const u32 grp = __match_any_sync(FULLMASK, cand ? key : 0x100u + lane);
+            bool dup = cand && __popc(grp) > 1;
+            if (__any_sync(FULLMASK, dup)) {
+                const u32 skey = (u32)((int)(signed char)key + 128);  // std::map<char,...> iterates signed chars ascending
+                // ---- can the whole merge run warp-parallel?  Yes when every member is a plain chain vertex (one
+                // in-edge, one unvisited out-edge, inline lists), no member is the target of another member, and a
+                // group has at most 6 members (the survivor's inline out-slots then hold every distinct target).
+                u32 x = NIL, cvx = 0, wgt = 0;
+                bool ok = true;
+                if (dup) {
+                    u8* r = g.base + (size_t)sl.dst * REC_UNIT;
+                    const u32 optr = ((const Hdr*)r)->out_ptr;
+                    wgt = (u32)((const Hdr*)r)->weight;
+                    const OSlot s0 = *(const OSlot*)(r + REC_OUT_OFF);
+                    x = s0.dst; cvx = s0.cv;
+                    ok = d.y == 0x10001u && optr == gv_inline_out(sl.dst) && !(cvx & VISBIT) && __popc(grp) <= 6;
+                }
+                bool clash = false;
+                for (u32 m = __ballot_sync(FULLMASK, dup); m; m &= m - 1) {
+                    const u32 xj = __shfl_sync(FULLMASK, x, __ffs((int)m) - 1);
+                    clash |= dup && sl.dst == xj;
+                }
+                if (!__any_sync(FULLMASK, (dup && !ok) || clash)) {
+                    u32 removed = 0;
+                    bool pending = dup;
+                    for (;;) {
+                        const u32 k = __reduce_min_sync(FULLMASK, pending ? skey : 0xFFFFFFFFu);
+                        if (k == 0xFFFFFFFFu) break;
+                        const bool in_grp = pending && skey == k;
+                        const u32 M = __ballot_sync(FULLMASK, in_grp);
+                        const u32 la = (u32)__ffs((int)M) - 1;          // the survivor `an` = first member in list order
+                        const u32 an = __shfl_sync(FULLMASK, sl.dst, la);
+                        if (in_grp) {
+                            const bool is_a = lane == la;
+                            // :238-243  _g[*anii].count += _g[*ii].count;  _g[an].weight += _g[*ni].weight
+                            const u32 cvs = __reduce_add_sync(M, is_a ? 0u : (sl.cv & ~VISBIT));
+                            const u32 ws = __reduce_add_sync(M, is_a ? 0u : wgt);
+                            // :246-259  the members' out-edges move to `an`: one slot per distinct target, counts summed,
+                            // new targets in the order of the member that brings them
+                            const u32 Mx = __match_any_sync(M, x);
+                            const bool leader = lane == (u32)__ffs((int)Mx) - 1;
+                            const u32 Cx = __reduce_add_sync(Mx, cvx);
+                            const u32 newl = __ballot_sync(M, leader && !is_a);
+                            u8* ra = g.base + (size_t)an * REC_UNIT;
+                            if (is_a) {
+                                sl.cv += cvs;
+                                ((Hdr*)ra)->weight = (int)(wgt + ws);
+                                ((Hdr*)ra)->deg = 1u | ((1u + (u32)__popc(newl)) << 16);
+                                ((OSlot*)(ra + REC_OUT_OFF))[0].cv = Cx;
+                            } else if (leader) {
+                                OSlot ns;
+                                ns.dst = x; ns.cv = Cx;
+                                ((OSlot*)(ra + REC_OUT_OFF))[1 + __popc(newl & ((1u << lane) - 1u))] = ns;
+                            }
+                            // the in-list of each distinct target: the merged members leave (clear_vertex keeps the
+                            // order of the rest), `an` is appended unless it was a source already
+                            Hdr* hx = nullptr;
+                            u32* inx = nullptr;
+                            u32 xin = 0;
+                            if (leader) { hx = gv_hdr(g, x); xin = hx->deg & 0xFFFFu; inx = gv_in(g, hx->in_ptr); }
+                            for (u32 mm = M & ~(1u << la); mm; mm &= mm - 1) {
+                                const u32 j = (u32)__ffs((int)mm) - 1;
+                                const u32 nj = __shfl_sync(M, sl.dst, j);
+                                if (leader && ((Mx >> j) & 1u)) {
+                                    u32 i = 0;
+                                    while (i < xin && inx[i] != nj) i++;
+                                    if (i == xin) status = T_INTERNAL;
+                                    else { for (; i + 1 < xin; i++) inx[i] = inx[i + 1]; xin--; }
+                                }
+                            }
+                            if (leader) {
+                                if (!is_a) inx[xin++] = an;
+                                hx->deg = (hx->deg & 0xFFFF0000u) | xin;
+                            }
+                            // markForReaper(member) :260
+                            if (!is_a) *(uint2*)gv_hdr(g, sl.dst) = make_uint2((d.x & 0xFFFFu) | (NF_DELETED << 8), 0u);
+                        }
+                        removed |= M & ~(1u << la);
+                        pending = pending && !in_grp;
+                    }
+                    // u's out-list without the merged members, order kept
+                    const u32 surv = __ballot_sync(FULLMASK, have) & ~removed;
+                    if (have && !((removed >> lane) & 1u)) gv_out(g, hu.out_ptr)[__popc(surv & ((1u << lane) - 1u))] = sl;
+                    if (lane == 0) pu->deg = (hu.deg & 0xFFFFu) | ((u32)__popc(surv) << 16);
+                    if (__any_sync(FULLMASK, status != T_OK)) status = T_INTERNAL;
+                } else {
+                    // groups in ascending key order, members in list order, on lane 0
+                    for (;;) {
+                        const u32 k = __reduce_min_sync(FULLMASK, dup ? skey : 0xFFFFFFFFu);
+                        if (k == 0xFFFFFFFFu) break;
+                        const bool in_grp = dup && skey == k;
+                        u32 members = __ballot_sync(FULLMASK, in_grp);
+                        const u32 an = __shfl_sync(FULLMASK, sl.dst, __ffs((int)members) - 1);
+                        members &= members - 1;
+                        while (members) {
+                            const u32 ni = __shfl_sync(FULLMASK, sl.dst, __ffs((int)members) - 1);
+                            members &= members - 1;
+                            if (lane == 0 && g.status == T_OK) m2_merge_out_member(g, an, ni);
+                        }
+                        if (in_grp) dup = false;
+                    }
+                    __syncwarp();
+                    status = __shfl_sync(FULLMASK, g.status, 0);
+                }
+                __syncwarp();
+                hu = *pu;  // merging only removed out-edges of u (and changed their targets)
+                nout = hu.deg >> 16;
+                have = lane < nout;
+                sl.dst = 0; sl.cv = 0;
+                d = make_uint2(0u, 0u);
+                if (have) { sl = gv_out(g, hu.out_ptr)[lane]; d = *(const uint2*)gv_hdr(g, sl.dst); }
+            }
+        }
+        {
+            const bool fresh = have && !(sl.cv & VISBIT);
+            if (fresh) gv_out(g, hu.out_ptr)[lane].cv = sl.cv | VISBIT;
+            u32 bfv = d.x + (fresh ? 0x10000u : 0u);
+            const bool ready = have && (bfv >> 16) == (d.y & 0xFFFFu);  // notVisited == 0
+            if (ready && (bfv & (NF_QUEUED << 8))) status = T_INTERNAL;
+            if (ready) bfv |= NF_QUEUED << 8;
+            if (have && bfv != d.x) gv_hdr(g, sl.dst)->bfv = bfv;
+            m2_queue_append(g, __ballot_sync(FULLMASK, ready), ready, sl.dst, tail, lane);
+            if (__any_sync(FULLMASK, status != T_OK)) status = T_INTERNAL;
+        }
+        __syncwarp();
+        head = pu->best;
+    }
+    if (lane == 0) {
+        a.tgt_pool_top[t] = g.pool_top;
+        if (status == T_OK) status = g.status;
+        if (status != T_OK) a.tgt_status[t] = status;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4: bestPath (:375-459) and the two consensus() forms (:285-373), one warp per target.
+// Reverse topological sweep from exit: lane j scores out-edge j of the popped vertex (its target's header is one
+// 32-byte load), a warp max + ballot picks the FIRST maximum in list order (the reference's strict `>` scan),
+// then lane j counts in-edge j down at its source and the sources that became ready are appended in list order.
+__device__ __forceinline__ u32 f2ord(float f) {  // order-preserving map float -> u32
+    const u32 u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_best_path2(Serial2Args a) {
+    u32 t;
+    T2Ctx c;
+    if (!warp2_setup(a, t, c)) return;
+    const GV& g = c.g;
+    const u32 lane = threadIdx.x & 31;
+    const u32 L = a.tgt_tlen[t], ENTER = 0, EXIT = 2 * (L + 1), nV = a.tgt_nv[t];
+    u32 head = EXIT, tail = EXIT;
+    if (lane == 0) gv_hdr(g, EXIT)->best = NIL;
+    __syncwarp();
+    while (head != NIL) {
+        const u32 n = head;
+        Hdr* pn = gv_hdr(g, n);
+        const Hdr hn = *pn;
+        const u32 nout = hn.deg >> 16, nin = hn.deg & 0xFFFFu;
+        // ---- the best out-edge: first maximum of the per-edge scores in list order
+        float best_score = -FLT_MAX;
+        u32 best_dst = NIL;
+        for (u32 b0 = 0; b0 < nout; b0 += 32) {
+            const bool have = b0 + lane < nout;
+            float ns = -FLT_MAX;
+            u32 dst = NIL;
+            if (have) {
+                const OSlot s = gv_out(g, hn.out_ptr)[b0 + lane];
+                const Hdr hd = *gv_hdr(g, s.dst);
+                dst = s.dst;
+                // bestPath :402-409: a backbone vertex no read agrees with costs 10; otherwise count - coverage/2
+                if ((hd.bfv & (NF_BACKBONE << 8)) && hd.weight == 1) ns = __fsub_rn(hd.score, 10.0f);
+                else ns = __fadd_rn(__fsub_rn((float)(int)(s.cv & ~VISBIT), __fmul_rn((float)hd.cov, 0.5f)), hd.score);
+            }
+            const u32 key = have ? f2ord(ns) : 0u;
+            const u32 mx = __reduce_max_sync(FULLMASK, key);
+            const u32 who = __ffs((int)__ballot_sync(FULLMASK, have && key == mx)) - 1;
+            const float cs = __shfl_sync(FULLMASK, ns, who);
+            const u32 cd = __shfl_sync(FULLMASK, dst, who);
+            if (cs > best_score) { best_score = cs; best_dst = cd; }  // strict >: an earlier chunk's maximum stays
+        }
+        // ---- count this vertex off at its predecessors; those with all successors scored join the queue
+        for (u32 b0 = 0; b0 < nin; b0 += 32) {
+            const bool have = b0 + lane < nin;
+            u32 s = NIL;
+            bool ready = false;
+            if (have) {
+                s = gv_in(g, hn.in_ptr)[b0 + lane];
+                Hdr* hs = gv_hdr(g, s);
+                const u32 k = (u32)(hs->cnt + 1);
+                hs->cnt = (int)k;
+                ready = k == (hs->deg >> 16);
+                if (ready) hs->best = NIL;
+            }
+            __syncwarp();
+            m2_queue_append(g, __ballot_sync(FULLMASK, ready), ready, s, tail, lane);
+        }
+        __syncwarp();
+        const u32 nx = pn->best;
+        __syncwarp();
+        if (lane == 0) {
+            pn->score = best_dst != NIL ? best_score : 0.0f;  // an absent map key reads as 0.0f (:401)
+            pn->best = best_dst;                              // from here on: the successor on the best path
+            pn->bfv = hn.bfv | (NF_SCORED << 8);
+        }
+        __syncwarp();
+        head = nx;
+    }
+    if (lane != 0) return;
+    // walk the best path and cut it into min-weight runs (consensus :285-373)
+    u8* cons = a.cons + a.cons_off[t];
+    int* fr = a.frags + 2 * a.frag_off[t];
+    const u32 fcap = a.frag_cap[t];
+    const u32 eb = n_base(gv_hdr(g, ENTER)->bfv), xb = n_base(gv_hdr(g, EXIT)->bfv);
+    const int minw = (int)a.min_weight;
+    const bool single = a.flags & F_SINGLE;
+    int offs = 0, idx = 0, best_offs = 0, length = 0;
+    bool met = false;
+    u32 nfrag = 0, steps = 0, prev = ENTER, status = T_OK;
+    for (;;) {
+        const Hdr hp = *gv_hdr(g, prev);
+        const u32 b = hp.bfv & 0xFFu;
+        const int w = hp.weight;
+        if (b != eb && b != xb) {
+            cons[idx] = (u8)b;
+            if (!met && w >= minw) { offs = idx; met = true; }
+            else if (met && w < minw) {
+                met = false;
+                if (single) { if (idx - offs > length) { best_offs = offs; length = idx - offs; } }
+                else if ((u32)(idx - offs) >= a.min_len) {
+                    if (nfrag < fcap) { fr[2 * nfrag] = offs; fr[2 * nfrag + 1] = idx; nfrag++; } else status = T_INTERNAL;
+                }
+            }
+            idx++;
+        }
+        if (!(hp.bfv & (NF_SCORED << 8)) || hp.best == NIL) break;
+        prev = hp.best;
+        if (++steps > nV) { status = T_INTERNAL; break; }
+    }
+    if (single) {
+        if (met && idx - offs > length) { best_offs = offs; length = idx - offs; }
+        fr[0] = best_offs; fr[1] = best_offs + length; nfrag = 1;
+    } else if (met && (u32)(idx - offs) >= a.min_len) {
+        if (nfrag < fcap) { fr[2 * nfrag] = offs; fr[2 * nfrag + 1] = idx; nfrag++; } else status = T_INTERNAL;
+    }
+    a.tgt_cons_len[t] = (u32)idx;
+    a.tgt_nfrag[t] = nfrag;
+    if (status != T_OK) { a.tgt_status[t] = status; a.tgt_nfrag[t] = 0; }
+}
