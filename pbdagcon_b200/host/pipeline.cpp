@@ -356,6 +356,10 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         } else if (!rc) {
             text.clear();
             for (uint32_t t = 0; t < r.n_targets; t++) {
+                if (r.tgt_status[t] > DGC_T_SKIPPED)  // rejected, never silently: the reference would walk off its vertex array here
+                    fprintf(stderr, "pbdagcon: target %s rejected (status %u: %s)\n", hb->ids[t].c_str(), r.tgt_status[t],
+                            r.tgt_status[t] == DGC_T_BAD_ALIGNMENT ? "an alignment runs off the backbone" :
+                            r.tgt_status[t] == DGC_T_TOO_MANY_ALNS ? "too many alignments" : "internal");
                 for (uint32_t f = r.tgt_frag_begin[t]; f < r.tgt_frag_begin[t + 1]; f++) {
                     text.push_back('>');
                     text += hb->ids[t];
