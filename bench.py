@@ -7,7 +7,7 @@ backbone x 30x coverage, 15 % indel-dominated error, pbdagcon flags -c 8 (-m 500
 
   value     corrected Mbp/s with the packed batch already resident in HBM (dgc_upload + dgc_run)
   e2e       the same metric through the reference-facing call (dgc_submit/dgc_collect) from pinned HOST buffers:
-            H2D of every sub-batch, kernels, D2H of the CnsResults inside the timed region
+            staged H2D of the batch, kernels, D2H of the CnsResults inside the timed region
   --impl reference   the reference's own CPU code (oracle/_ref/libdagcon_ref.so = its unmodified sources) on all
             host threads, on a bounded sample of the same workload.
 """
@@ -217,7 +217,7 @@ def run_gpu(args):
     h2d_bytes = sum(int(p.arena.size) + 4 * (2 * p.n_targets + 1) + 24 * p.n_alns + 8 * p.n_alns for p in sub_pb)
 
     eng = api.Consensus(min_cov=MIN_COV, min_len=MIN_LEN, trim=TRIM, device=dev, targets_per_warp=args.tpw,
-                        scratch_bytes=args.scratch_gb << 30)
+                        scratch_bytes=args.scratch_gb << 30, flags=args.flags)
     # ---- arm 1: HBM-resident
     db = eng.upload(whole)
     if len(subs) > 1:
@@ -256,7 +256,10 @@ def run_gpu(args):
     value = tot_bases * args.steps / dev_s / 1e6
 
     # ---- arm 2: end to end from pinned host buffers through submit/collect (two sub-batches in flight)
+    e2e_t0 = [0.0]
+
     def e2e_pass():
+        e2e_t0[0] = time.perf_counter()
         nb = 0
         d2h = 0
         nsub, sent, got = len(sub_pb), 0, 0
@@ -266,6 +269,10 @@ def run_gpu(args):
                 sent += 1
             r = eng.collect(copy=False)
             got += 1
+            if args.e2e_trace:
+                tmx = eng.timings()
+                print("e2e sub-batch", got, {k: round(v, 1) for k, v in tmx.items() if k.startswith("ms_")},
+                      "t=%.1f ms" % ((time.perf_counter() - e2e_t0[0]) * 1e3), file=sys.stderr)
             nb += int(np.ctypeslib.as_array(r.frag_seq_len, (r.n_frags,)).astype(np.int64).sum()) if r.n_frags else 0
             d2h += int(r.seq_bytes) + 8 * r.n_frags + 16 * r.n_targets
         return nb, d2h
@@ -350,11 +357,16 @@ def main():
     ap.add_argument("--L", type=int, default=8000)
     ap.add_argument("--cov", type=float, default=30)
     ap.add_argument("--seed", type=int, default=2)
-    ap.add_argument("--sub", type=int, default=2500, help="targets per submitted sub-batch (e2e arm)")
+    ap.add_argument("--sub", type=int, default=0, help="targets per dgc_submit in the e2e arm (0 = the whole step in one "
+                    "submit: the library stages the upload itself)")
     ap.add_argument("--tpw", type=int, default=0, help="targets per warp in the serial kernels (0 = auto)")
-    ap.add_argument("--scratch-gb", type=int, default=48)
+    ap.add_argument("--scratch-gb", type=int, default=72)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-trace", action="store_true", help="print the device timings of every collected sub-batch")
+    ap.add_argument("--flags", type=int, default=0, help="extra dgc_opts.flags (tuning, e.g. 256 = no prefetch)")
     args = ap.parse_args()
+    if args.sub <= 0:
+        args.sub = args.targets
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -47,6 +47,7 @@ extern "C" {
 #define DGC_F_NO_MERGE 4u     /* skip mergeNodes */
 #define DGC_F_SINGLE 8u       /* consensus(minWeight) -> one longest run (AlnGraphBoost.cpp:285-325)
                                  instead of consensus(seqs,minWeight,minLen) (:327-373) */
+#define DGC_F_NO_PREFETCH 256u /* tuning/diagnostic: the graph sweeps do not prefetch vertex records (results identical) */
 
 /* Replaces ProgramOpts (src/cpp/ProgramOpts.hpp:8-36) for this path. */
 typedef struct dgc_opts {
@@ -56,7 +57,7 @@ typedef struct dgc_opts {
     uint32_t flags;         /* DGC_F_* */
     int32_t device;         /* CUDA device ordinal */
     uint32_t targets_per_warp; /* serial graph kernels: 0 = auto */
-    uint64_t scratch_bytes; /* HBM budget for the per-chunk graph arena; 0 = default (24 GiB) */
+    uint64_t scratch_bytes; /* HBM budget for the per-chunk graph arena; 0 = default (72 GiB: 10 000 targets of 8 kb x 30x in one chunk) */
 } dgc_opts;
 
 /* Packed targets (SoA).  Host pointers; pinned memory (dgc_host_alloc) makes the H2D copy async.
@@ -79,7 +80,7 @@ typedef struct dgc_batch {
 
 /* Replaces std::vector<CnsResult> per target (src/cpp/AlnGraphBoost.hpp CnsResult; filled at
  * AlnGraphBoost.cpp:327-373).  Memory is owned by the handle and stays valid until the next
- * dgc_collect / dgc_run on it, or dgc_destroy. */
+ * dgc_submit / dgc_collect / dgc_consensus / dgc_run on it, or dgc_destroy. */
 typedef struct dgc_results {
     uint32_t n_targets;
     uint32_t n_frags;

@@ -11,7 +11,9 @@
 
 #include <algorithm>
 #include <condition_variable>
+#include <deque>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -33,6 +35,19 @@ struct DevBuf {
         cudaError_t e = cudaMalloc(&p, want);
         if (e != cudaSuccess) { e = cudaMalloc(&p, bytes + 256); want = bytes + 256; }
         if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    // grow without losing the first `live` bytes (device-wide sync: only taken when an estimate fell short)
+    cudaError_t ensure_keep(size_t bytes, size_t live) {
+        if (bytes <= cap) return cudaSuccess;
+        void* np = nullptr;
+        const size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&np, want);
+        if (e != cudaSuccess) return e;
+        if (p && live) e = cudaMemcpy(np, p, std::min(live, cap), cudaMemcpyDeviceToDevice);
+        else e = cudaDeviceSynchronize();
+        if (p) cudaFree(p);
+        p = np; cap = want;
         return e;
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
@@ -88,6 +103,7 @@ struct Slot {
     dgc_handle* h = nullptr;
     int index = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;  // staged uploads: the arena pieces travel here while s.stream computes
     dgc_dbatch db;  // device copy of a submitted batch
     HostBuf h_norm_off;
     // per-alignment work arrays
@@ -115,6 +131,8 @@ struct Slot {
     std::condition_variable cv;
     enum State { IDLE, QUEUED, RUNNING, DONE, STOP } state = IDLE;
     dgc_batch pending{};  // copied at submit: only the arrays it points to must outlive the call
+    uint64_t seq = 0;     // submit sequence number of `pending`
+    uint64_t hint[5] = {0, 0, 0, 0, 0};  // arena needs (units, positions, cons, frags, scratch) of the last staged batch that fit one chunk
     int rc = 0;
     std::string err;
 };
@@ -127,10 +145,23 @@ struct dgc_handle {
     int device = 0;
     int sm_count = 148;
     size_t build_smem_max = 0;
+    // staged uploads (run_staged): piece size and the smallest arena worth staging; DGC_STAGE_PIECE_BYTES /
+    // DGC_STAGE_MIN_BYTES override them (tests stage tiny batches)
+    uint64_t stage_piece_bytes = 384ull << 20, stage_min_bytes = 64ull << 20;
     std::string err;
     Slot slots[NSLOT];
     uint64_t submitted = 0, collected = 0;
     dgc_timings last_tm{};
+    // H2D copies of submitted batches run one at a time, in submit order: batch n's kernels start as soon as its own
+    // bytes have landed while batch n+1 is on the wire (concurrent copies would share the link and all land late)
+    std::mutex h2d_mu;
+    std::condition_variable h2d_cv;
+    uint64_t h2d_turn = 0;
+    // slots in flight, in submit order; a submit takes the lowest free slot so that a caller with one batch in flight
+    // keeps reusing one slot's arenas instead of growing all of them
+    std::mutex q_mu;
+    std::deque<int> inflight;
+    bool busy[NSLOT] = {};
 };
 
 namespace {
@@ -177,7 +208,7 @@ int validate_batch(const dgc_batch* b, std::string& err) {
 }
 
 // H2D of a batch into db (async on s.stream; host arrays must stay valid until the stream syncs)
-int upload_batch(Slot& s, const dgc_batch* b, dgc_dbatch& db, bool timed) {
+int upload_batch(Slot& s, const dgc_batch* b, dgc_dbatch& db, bool timed, bool with_arena = true) {
     db.T = b->n_targets; db.A = b->n_alns; db.has_bb = b->tgt_bb_off != nullptr; db.arena_bytes = b->arena_bytes;
     const size_t T = db.T, A = db.A;
     CU(db.tgt_tlen.ensure(4 * (T + 1))); CU(db.tgt_aln_begin.ensure(4 * (T + 1)));
@@ -210,7 +241,7 @@ int upload_batch(Slot& s, const dgc_batch* b, dgc_dbatch& db, bool timed) {
         CU(cudaMemcpyAsync(db.aln_t_off.p, b->aln_t_off, 8 * A, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(db.aln_norm_off.p, no, 8 * A, cudaMemcpyHostToDevice, st));
     }
-    if (b->arena_bytes) CU(cudaMemcpyAsync(db.arena.p, b->arena, b->arena_bytes, cudaMemcpyHostToDevice, st));
+    if (b->arena_bytes && with_arena) CU(cudaMemcpyAsync(db.arena.p, b->arena, b->arena_bytes, cudaMemcpyHostToDevice, st));
     if (timed) span_end(s);
     return DGC_OK;
 }
@@ -224,31 +255,168 @@ int ensure_alignment_arrays(Slot& s, const dgc_dbatch& db) {
     return DGC_OK;
 }
 
-int launch_normalize(Slot& s, const dgc_dbatch& db) {
+// K1 for alignments [k0, k1)
+int launch_normalize(Slot& s, const dgc_dbatch& db, uint32_t k0, uint32_t k1) {
     const dgc_opts& o = s.h->opts;
     NormArgs na;
     na.arena = db.arena.as<u8>(); na.aln_start = db.aln_start.as<u32>(); na.aln_len = db.aln_len.as<u32>();
     na.aln_q_off = db.aln_q_off.as<u64>(); na.aln_t_off = db.aln_t_off.as<u64>(); na.aln_norm_off = db.aln_norm_off.as<u64>();
-    na.n_alns = db.A; na.min_len = o.min_len; na.trim = o.trim; na.flags = o.flags;
+    na.n_alns = k1; na.aln_first = k0; na.min_len = o.min_len; na.trim = o.trim; na.flags = o.flags;
     na.norm = s.norm.as<u16>(); na.o_off = s.o_off.as<u64>(); na.o_len = s.o_len.as<u32>(); na.o_start = s.o_start.as<u32>();
     na.o_flags = s.o_flags.as<u32>(); na.o_nI = s.o_nI.as<u32>(); na.o_nE = s.o_nE.as<u32>(); na.o_tkept = s.o_tkept.as<u32>();
-    if (db.A) {
+    const uint32_t n = k1 - k0;
+    if (n) {
         if (o.flags & DGC_F_NO_NORMALIZE) {
             na.retry_only = 0;
-            k_normalize_trim<<<(db.A + 127) / 128, 128, 0, s.stream>>>(na);
+            k_normalize_trim<<<(n + 127) / 128, 128, 0, s.stream>>>(na);
             s.tm.launches++;
         } else {
             na.retry_only = 1;
-            k_normalize_warp<<<(db.A + NW_WARPS - 1) / NW_WARPS, NW_WARPS * 32, 0, s.stream>>>(na);
-            k_normalize_trim<<<(db.A + 127) / 128, 128, 0, s.stream>>>(na);  // the few the warp kernel handed back
+            k_normalize_warp<<<(n + NW_WARPS - 1) / NW_WARPS, NW_WARPS * 32, 0, s.stream>>>(na);
+            k_normalize_trim<<<(n + 127) / 128, 128, 0, s.stream>>>(na);  // the few the warp kernel handed back
             s.tm.launches += 2;
         }
     }
     CU(cudaGetLastError());
     return DGC_OK;
 }
+int launch_normalize(Slot& s, const dgc_dbatch& db) { return launch_normalize(s, db, 0, db.A); }
+
+// min-coverage filter and graph sizes for targets [t0, t1)
+int launch_plan(Slot& s, const dgc_dbatch& db, uint32_t t0, uint32_t t1) {
+    const dgc_opts& o = s.h->opts;
+    PlanArgs pa;
+    pa.n_targets = t1; pa.t_first = t0; pa.min_cov = o.min_cov; pa.tgt_tlen = db.tgt_tlen.as<u32>(); pa.tgt_aln_begin = db.tgt_aln_begin.as<u32>();
+    pa.a_start = s.o_start.as<u32>(); pa.a_flags = s.o_flags.as<u32>(); pa.a_nI = s.o_nI.as<u32>(); pa.a_nE = s.o_nE.as<u32>();
+    pa.a_tkept = s.o_tkept.as<u32>(); pa.a_len = s.o_len.as<u32>();
+    pa.tgt_status = s.t_status.as<u32>(); pa.tgt_V = s.t_V.as<u32>(); pa.tgt_E = s.t_E.as<u32>(); pa.tgt_cols = s.t_cols.as<u64>();
+    if (t1 > t0) k_target_plan<<<(t1 - t0 + 127) / 128, 128, 0, s.stream>>>(pa);
+    s.tm.launches++;
+    CU(cudaGetLastError());
+    return DGC_OK;
+}
 
 struct Chunk { uint32_t first, count; uint64_t nUnits, nPos, nCons, nFrag, nGs; uint32_t maxL2; };
+
+// K2 for targets [first, first + count) of the current chunk (their arena offsets are on the device already)
+int launch_build(Slot& s, dgc_dbatch& db, uint32_t first, uint32_t count, uint32_t maxL2) {
+    dgc_handle* h = s.h;
+    cudaStream_t st = s.stream;
+    Build2Args ba;
+    ba.first = first; ba.tgt_tlen = db.tgt_tlen.as<u32>(); ba.tgt_aln_begin = db.tgt_aln_begin.as<u32>();
+    ba.tgt_bb_off = db.has_bb ? db.tgt_bb_off.as<u64>() : nullptr; ba.arena = db.arena.as<u8>();
+    ba.tgt_status = s.t_status.as<u32>(); ba.rec_off = s.rec_off.as<u64>(); ba.tgt_V = s.t_V.as<u32>();
+    ba.pool_cap = s.pool_cap.as<u32>(); ba.acc_off = s.pos_off.as<u64>();
+    ba.norm = s.norm.as<u16>(); ba.a_off = s.o_off.as<u64>(); ba.a_len = s.o_len.as<u32>();
+    ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>();
+    ba.rec = s.rec.as<u8>();
+    ba.tgt_status_out = s.t_status.as<u32>(); ba.tgt_nv = s.t_nv.as<u32>(); ba.tgt_pool_top = s.t_pool_top.as<u32>();
+    // per-position running sums: 9 B per position in shared memory when the longest backbone of the chunk fits
+    ba.smem_positions = (uint32_t)std::min<uint64_t>(maxL2, h->build_smem_max / 9);
+    ba.gacc = s.gacc.as<u8>();
+    const size_t build_smem = (9ull * ba.smem_positions + 15) & ~15ull;
+    span_begin(s, PH_BUILD);
+    k_build_graph2<<<count, BT, build_smem, st>>>(ba);
+    s.tm.launches++;
+    CU(cudaGetLastError());
+    span_end(s);
+    return DGC_OK;
+}
+
+// K3, K4 and the output compaction for one chunk.  stop_after: 1 merge only, 2 everything.
+int launch_serial(Slot& s, dgc_dbatch& db, const Chunk& c, int stop_after) {
+    const dgc_opts& o = s.h->opts;
+    cudaStream_t st = s.stream;
+
+    Serial2Args sa;
+    sa.first = c.first; sa.count = c.count;
+    sa.flags = o.flags; sa.min_weight = o.min_cov; sa.min_len = o.min_len;
+    sa.tgt_tlen = db.tgt_tlen.as<u32>(); sa.tgt_aln_begin = db.tgt_aln_begin.as<u32>(); sa.tgt_status = s.t_status.as<u32>();
+    sa.rec_off = s.rec_off.as<u64>(); sa.tgt_V = s.t_V.as<u32>();
+    sa.pool_cap = s.pool_cap.as<u32>(); sa.tgt_pool_top = s.t_pool_top.as<u32>(); sa.tgt_nv = s.t_nv.as<u32>();
+    sa.rec = s.rec.as<u8>();
+    sa.gscratch = s.gscratch.as<u32>(); sa.gscratch_off = s.gs_off.as<u64>(); sa.gscratch_cap = s.gs_cap.as<u32>();
+    sa.cons = s.cons.as<u8>(); sa.cons_off = s.cons_off.as<u64>(); sa.frags = s.frags.as<int>(); sa.frag_off = s.frag_off.as<u64>();
+    sa.frag_cap = s.frag_cap.as<u32>(); sa.tgt_cons_len = s.t_cons_len.as<u32>(); sa.tgt_nfrag = s.t_nfrag.as<u32>();
+    const uint32_t warps_per_block = WARP_KERNEL_THREADS / 32;   // one warp per target
+    const uint32_t grid = (c.count + warps_per_block - 1) / warps_per_block;
+    if (!(o.flags & DGC_F_NO_MERGE)) {
+        span_begin(s, PH_MERGE);
+        k_merge_nodes2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
+        s.tm.launches++;
+        CU(cudaGetLastError());
+        span_end(s);
+    }
+    if (stop_after < 2) return DGC_OK;
+    span_begin(s, PH_PATH);
+    k_best_path2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
+    s.tm.launches++;
+    CU(cudaGetLastError());
+    span_end(s);
+    span_begin(s, PH_COMPACT);
+    // scan over the chunk's targets, chained through `totals` so chunks append to one output
+    k_scan_outputs<<<1, 1024, 0, st>>>(c.count, s.t_status.as<u32>() + c.first, s.t_cons_len.as<u32>() + c.first,
+                                       s.t_nfrag.as<u32>() + c.first, s.t_cons_coff.as<u64>() + c.first,
+                                       s.t_frag_coff.as<u32>() + c.first, s.totals.as<u64>());
+    k_compact<<<c.count, 128, 0, st>>>(c.count, s.t_status.as<u32>() + c.first, s.t_cons_len.as<u32>() + c.first,
+                                       s.t_nfrag.as<u32>() + c.first, s.cons.as<u8>(), s.cons_off.as<u64>() + c.first,
+                                       s.frags.as<int>(), s.frag_off.as<u64>() + c.first, s.t_cons_coff.as<u64>() + c.first,
+                                       s.t_frag_coff.as<u32>() + c.first, s.out_cons.as<u8>(), s.out_frags.as<int>());
+    s.tm.launches += 2;
+    CU(cudaGetLastError());
+    span_end(s);
+    return DGC_OK;
+}
+
+// D2H of the compacted results and the CnsResult records in target order
+int fetch_results(Slot& s, dgc_dbatch& db) {
+    const size_t T = db.T;
+    cudaStream_t st = s.stream;
+    // ---- D2H of the compacted results
+    span_begin(s, PH_D2H);
+    CU(s.r_status.ensure(4 * (T + 1))); CU(s.r_cons_coff.ensure(8 * (T + 1))); CU(s.r_frag_coff.ensure(4 * (T + 1)));
+    CU(s.r_totals.ensure(64)); CU(s.r_nfrag.ensure(4 * (T + 1)));
+    CU(cudaMemcpyAsync(s.r_nfrag.p, s.t_nfrag.p, 4 * T, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(s.r_status.p, s.t_status.p, 4 * T, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(s.r_cons_coff.p, s.t_cons_coff.p, 8 * T, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(s.r_frag_coff.p, s.t_frag_coff.p, 4 * T, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(s.r_totals.p, s.totals.p, 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint64_t tot_cons = s.r_totals.as<uint64_t>()[0], tot_frag = s.r_totals.as<uint64_t>()[1];
+    CU(s.r_cons.ensure(tot_cons + 16)); CU(s.r_frags.ensure(8 * tot_frag + 16));
+    if (tot_cons) CU(cudaMemcpyAsync(s.r_cons.p, s.out_cons.p, tot_cons, cudaMemcpyDeviceToHost, st));
+    if (tot_frag) CU(cudaMemcpyAsync(s.r_frags.p, s.out_frags.p, 8 * tot_frag, cudaMemcpyDeviceToHost, st));
+    span_end(s);
+    CU(cudaStreamSynchronize(st));
+
+    // ---- CnsResult records in target order
+    const uint32_t* rs = s.r_status.as<uint32_t>();
+    const uint64_t* cc = s.r_cons_coff.as<uint64_t>();
+    const uint32_t* fc = s.r_frag_coff.as<uint32_t>();
+    const int32_t* fr = s.r_frags.as<int32_t>();
+    const uint32_t* rn = s.r_nfrag.as<uint32_t>();
+    s.res_r0.reserve(tot_frag); s.res_r1.reserve(tot_frag); s.res_seq_off.reserve(tot_frag); s.res_seq_len.reserve(tot_frag);
+    for (size_t t = 0; t < T; t++) {
+        s.res_frag_begin[t] = (uint32_t)s.res_r0.size();
+        if (rs[t] != T_OK) continue;
+        const uint32_t f0 = fc[t], nf = rn[t];
+        for (uint32_t i = 0; i < nf; i++) {
+            const int32_t r0 = fr[2 * (size_t)(f0 + i)], r1 = fr[2 * (size_t)(f0 + i) + 1];
+            s.res_r0.push_back(r0); s.res_r1.push_back(r1);
+            s.res_seq_off.push_back(cc[t] + (uint64_t)r0);
+            s.res_seq_len.push_back((uint32_t)(r1 - r0));
+        }
+    }
+    s.res_frag_begin[T] = (uint32_t)s.res_r0.size();
+    s.results.n_frags = (uint32_t)s.res_r0.size();
+    s.results.tgt_status = rs;
+    s.results.tgt_frag_begin = s.res_frag_begin.data();
+    s.results.frag_range0 = s.res_r0.data(); s.results.frag_range1 = s.res_r1.data();
+    s.results.frag_seq_off = s.res_seq_off.data(); s.results.frag_seq_len = s.res_seq_len.data();
+    s.results.seq_arena = s.r_cons.as<uint8_t>(); s.results.seq_bytes = tot_cons;
+    return DGC_OK;
+}
+
 
 // The whole hot path for a resident batch.  stop_after: 0 build, 1 merge, 2 everything.
 int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) {
@@ -281,14 +449,8 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     span_end(s);
 
     span_begin(s, PH_COUNT);
-    PlanArgs pa;
-    pa.n_targets = db.T; pa.min_cov = o.min_cov; pa.tgt_tlen = db.tgt_tlen.as<u32>(); pa.tgt_aln_begin = db.tgt_aln_begin.as<u32>();
-    pa.a_start = s.o_start.as<u32>(); pa.a_flags = s.o_flags.as<u32>(); pa.a_nI = s.o_nI.as<u32>(); pa.a_nE = s.o_nE.as<u32>();
-    pa.a_tkept = s.o_tkept.as<u32>(); pa.a_len = s.o_len.as<u32>();
-    pa.tgt_status = s.t_status.as<u32>(); pa.tgt_V = s.t_V.as<u32>(); pa.tgt_E = s.t_E.as<u32>(); pa.tgt_cols = s.t_cols.as<u64>();
-    k_target_plan<<<(db.T + 127) / 128, 128, 0, st>>>(pa);
-    s.tm.launches++;
-    CU(cudaGetLastError());
+    rc = launch_plan(s, db, 0, db.T);
+    if (rc) return rc;
     span_end(s);
 
     uint32_t* hp_status = s.hp_plan_in.as<uint32_t>();
@@ -310,7 +472,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     uint32_t* p_fcap = (uint32_t*)(p_gs + (T + 1));
     uint32_t* p_gcap = p_fcap + (T + 1);
     uint32_t* p_pcap = p_gcap + (T + 1);
-    uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (32ull << 30);
+    uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
     std::vector<Chunk> chunks;
     Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
     auto chunk_bytes = [](const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; };
@@ -370,109 +532,304 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     CU(cudaMemsetAsync(s.t_nfrag.p, 0, 4 * (T + 1), st));
 
     for (auto& c : chunks) {
-        Build2Args ba;
-        ba.first = c.first; ba.tgt_tlen = db.tgt_tlen.as<u32>(); ba.tgt_aln_begin = db.tgt_aln_begin.as<u32>();
-        ba.tgt_bb_off = db.has_bb ? db.tgt_bb_off.as<u64>() : nullptr; ba.arena = db.arena.as<u8>();
-        ba.tgt_status = s.t_status.as<u32>(); ba.rec_off = s.rec_off.as<u64>(); ba.tgt_V = s.t_V.as<u32>();
-        ba.pool_cap = s.pool_cap.as<u32>(); ba.acc_off = s.pos_off.as<u64>();
-        ba.norm = s.norm.as<u16>(); ba.a_off = s.o_off.as<u64>(); ba.a_len = s.o_len.as<u32>();
-        ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>();
-        ba.rec = s.rec.as<u8>();
-        ba.tgt_status_out = s.t_status.as<u32>(); ba.tgt_nv = s.t_nv.as<u32>(); ba.tgt_pool_top = s.t_pool_top.as<u32>();
-        // per-position running sums: 9 B per position in shared memory when the longest backbone of the chunk fits
-        ba.smem_positions = (uint32_t)std::min<uint64_t>(c.maxL2, h->build_smem_max / 9);
-        ba.gacc = s.gacc.as<u8>();
-        const size_t build_smem = (9ull * ba.smem_positions + 15) & ~15ull;
-        span_begin(s, PH_BUILD);
-        k_build_graph2<<<c.count, BT, build_smem, st>>>(ba);
-        s.tm.launches++;
-        CU(cudaGetLastError());
-        span_end(s);
+        rc = launch_build(s, db, c.first, c.count, c.maxL2);
+        if (rc) return rc;
         if (stop_after == 0) continue;
-
-        Serial2Args sa;
-        sa.first = c.first; sa.count = c.count;
-        sa.flags = o.flags; sa.min_weight = o.min_cov; sa.min_len = o.min_len;
-        sa.tgt_tlen = db.tgt_tlen.as<u32>(); sa.tgt_aln_begin = db.tgt_aln_begin.as<u32>(); sa.tgt_status = s.t_status.as<u32>();
-        sa.rec_off = s.rec_off.as<u64>(); sa.tgt_V = s.t_V.as<u32>();
-        sa.pool_cap = s.pool_cap.as<u32>(); sa.tgt_pool_top = s.t_pool_top.as<u32>(); sa.tgt_nv = s.t_nv.as<u32>();
-        sa.rec = s.rec.as<u8>();
-        sa.gscratch = s.gscratch.as<u32>(); sa.gscratch_off = s.gs_off.as<u64>(); sa.gscratch_cap = s.gs_cap.as<u32>();
-        sa.cons = s.cons.as<u8>(); sa.cons_off = s.cons_off.as<u64>(); sa.frags = s.frags.as<int>(); sa.frag_off = s.frag_off.as<u64>();
-        sa.frag_cap = s.frag_cap.as<u32>(); sa.tgt_cons_len = s.t_cons_len.as<u32>(); sa.tgt_nfrag = s.t_nfrag.as<u32>();
-        const uint32_t warps_per_block = WARP_KERNEL_THREADS / 32;   // one warp per target
-        const uint32_t grid = (c.count + warps_per_block - 1) / warps_per_block;
-        if (!(o.flags & DGC_F_NO_MERGE)) {
-            span_begin(s, PH_MERGE);
-            k_merge_nodes2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
-            s.tm.launches++;
-            CU(cudaGetLastError());
-            span_end(s);
-        }
-        if (stop_after < 2) continue;
-        span_begin(s, PH_PATH);
-        k_best_path2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
-        s.tm.launches++;
-        CU(cudaGetLastError());
-        span_end(s);
-        span_begin(s, PH_COMPACT);
-        // scan over the chunk's targets, chained through `totals` so chunks append to one output
-        k_scan_outputs<<<1, 1024, 0, st>>>(c.count, s.t_status.as<u32>() + c.first, s.t_cons_len.as<u32>() + c.first,
-                                           s.t_nfrag.as<u32>() + c.first, s.t_cons_coff.as<u64>() + c.first,
-                                           s.t_frag_coff.as<u32>() + c.first, s.totals.as<u64>());
-        k_compact<<<c.count, 128, 0, st>>>(c.count, s.t_status.as<u32>() + c.first, s.t_cons_len.as<u32>() + c.first,
-                                           s.t_nfrag.as<u32>() + c.first, s.cons.as<u8>(), s.cons_off.as<u64>() + c.first,
-                                           s.frags.as<int>(), s.frag_off.as<u64>() + c.first, s.t_cons_coff.as<u64>() + c.first,
-                                           s.t_frag_coff.as<u32>() + c.first, s.out_cons.as<u8>(), s.out_frags.as<int>());
-        s.tm.launches += 2;
-        CU(cudaGetLastError());
-        span_end(s);
+        rc = launch_serial(s, db, c, stop_after);
+        if (rc) return rc;
     }
     if (stop_after < 2) { CU(cudaStreamSynchronize(st)); return DGC_OK; }
+    return fetch_results(s, db);
+}
 
-    // ---- D2H of the compacted results
-    span_begin(s, PH_D2H);
-    CU(s.r_status.ensure(4 * (T + 1))); CU(s.r_cons_coff.ensure(8 * (T + 1))); CU(s.r_frag_coff.ensure(4 * (T + 1)));
-    CU(s.r_totals.ensure(64)); CU(s.r_nfrag.ensure(4 * (T + 1)));
-    CU(cudaMemcpyAsync(s.r_nfrag.p, s.t_nfrag.p, 4 * T, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(s.r_status.p, s.t_status.p, 4 * T, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(s.r_cons_coff.p, s.t_cons_coff.p, 8 * T, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(s.r_frag_coff.p, s.t_frag_coff.p, 4 * T, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(s.r_totals.p, s.totals.p, 32, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    const uint64_t tot_cons = s.r_totals.as<uint64_t>()[0], tot_frag = s.r_totals.as<uint64_t>()[1];
-    CU(s.r_cons.ensure(tot_cons + 16)); CU(s.r_frags.ensure(8 * tot_frag + 16));
-    if (tot_cons) CU(cudaMemcpyAsync(s.r_cons.p, s.out_cons.p, tot_cons, cudaMemcpyDeviceToHost, st));
-    if (tot_frag) CU(cudaMemcpyAsync(s.r_frags.p, s.out_frags.p, 8 * tot_frag, cudaMemcpyDeviceToHost, st));
-    span_end(s);
-    CU(cudaStreamSynchronize(st));
+// ------------------------------------------------------------------------------------------
+// Staged form of the same path for a batch that arrives from the host (dgc_submit).  The alignment strings are
+// the bulk of a batch (0.54 MB per 8 kb x 30x target); copying all of them before the first kernel leaves the SMs
+// idle for the whole transfer (100 ms for 10 000 targets).  When the targets' strings lie in the arena in target
+// order, a range of targets is a range of bytes: the arena travels in pieces on the slot's copy stream while the
+// compute stream normalises, sizes and builds the targets of each piece as soon as its bytes have landed.  The
+// latency-bound sweeps (mergeNodes, bestPath) then run once over every target that fits the arena, which is what
+// keeps ~10 000 chains in flight.
+struct Piece { uint32_t t0, t1, k0, k1; uint64_t b0, b1; cudaEvent_t copied; };
 
-    // ---- CnsResult records in target order
-    const uint32_t* rs = s.r_status.as<uint32_t>();
-    const uint64_t* cc = s.r_cons_coff.as<uint64_t>();
-    const uint32_t* fc = s.r_frag_coff.as<uint32_t>();
-    const int32_t* fr = s.r_frags.as<int32_t>();
-    const uint32_t* rn = s.r_nfrag.as<uint32_t>();
-    s.res_r0.reserve(tot_frag); s.res_r1.reserve(tot_frag); s.res_seq_off.reserve(tot_frag); s.res_seq_len.reserve(tot_frag);
-    for (size_t t = 0; t < T; t++) {
-        s.res_frag_begin[t] = (uint32_t)s.res_r0.size();
-        if (rs[t] != T_OK) continue;
-        const uint32_t f0 = fc[t], nf = rn[t];
-        for (uint32_t i = 0; i < nf; i++) {
-            const int32_t r0 = fr[2 * (size_t)(f0 + i)], r1 = fr[2 * (size_t)(f0 + i) + 1];
-            s.res_r0.push_back(r0); s.res_r1.push_back(r1);
-            s.res_seq_off.push_back(cc[t] + (uint64_t)r0);
-            s.res_seq_len.push_back((uint32_t)(r1 - r0));
+struct TurnMsg { dgc_handle* h; uint64_t next; };
+void release_h2d_turn_now(dgc_handle* h, uint64_t next) {
+    {
+        std::lock_guard<std::mutex> lk(h->h2d_mu);
+        h->h2d_turn = next;
+    }
+    h->h2d_cv.notify_all();
+}
+void CUDART_CB release_h2d_turn_cb(void* p) {  // host function on the copy stream: the batch's bytes have landed
+    TurnMsg* m = (TurnMsg*)p;
+    release_h2d_turn_now(m->h, m->next);
+    delete m;
+}
+
+// Splits a batch into about `want` target ranges of equal byte size; false when the arena is not laid out in
+// target order (then the batch is copied in one piece).
+bool split_pieces(const dgc_batch* b, uint32_t want, std::vector<Piece>& out) {
+    const uint32_t T = b->n_targets;
+    if (want < 2 || T < 2 * want) return false;
+    std::vector<uint64_t> hi(T);
+    uint64_t prev_hi = 0;
+    for (uint32_t t = 0; t < T; t++) {
+        uint64_t lo = ~0ull, h = 0;
+        if (b->tgt_bb_off) { lo = b->tgt_bb_off[t]; h = lo + b->tgt_tlen[t]; }
+        for (uint32_t k = b->tgt_aln_begin[t]; k < b->tgt_aln_begin[t + 1]; k++) {
+            const uint64_t n = b->aln_len[k], q = b->aln_q_off[k], tt = b->aln_t_off[k];
+            lo = std::min(lo, std::min(q, tt));
+            h = std::max(h, std::max(q, tt) + n);
+        }
+        if (lo == ~0ull) { lo = prev_hi; h = prev_hi; }
+        if (lo < prev_hi) return false;
+        prev_hi = std::max(prev_hi, h);
+        hi[t] = prev_hi;
+    }
+    const uint64_t per = b->arena_bytes / want + 1;
+    Piece p{0, 0, 0, 0, 0, 0, nullptr};
+    for (uint32_t t = 0; t < T; t++) {
+        if (hi[t] - p.b0 >= per || t + 1 == T) {
+            p.t1 = t + 1; p.k1 = b->tgt_aln_begin[t + 1];
+            p.b1 = t + 1 == T ? b->arena_bytes : hi[t];
+            out.push_back(p);
+            p = Piece{t + 1, 0, p.k1, 0, p.b1, 0, nullptr};
         }
     }
-    s.res_frag_begin[T] = (uint32_t)s.res_r0.size();
-    s.results.n_frags = (uint32_t)s.res_r0.size();
-    s.results.tgt_status = rs;
-    s.results.tgt_frag_begin = s.res_frag_begin.data();
-    s.results.frag_range0 = s.res_r0.data(); s.results.frag_range1 = s.res_r1.data();
-    s.results.frag_seq_off = s.res_seq_off.data(); s.results.frag_seq_len = s.res_seq_len.data();
-    s.results.seq_arena = s.r_cons.as<uint8_t>(); s.results.seq_bytes = tot_cons;
-    return DGC_OK;
+    return out.size() >= 2;
+}
+
+uint64_t chunk_bytes(const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; }
+
+int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
+    dgc_handle* h = s.h;
+    const dgc_opts& o = h->opts;
+    dgc_dbatch& db = s.db;
+    cudaStream_t st = s.stream, cs = s.copy_stream;
+    bool turn_released = false;
+    auto fail = [&](int rc) {
+        if (!turn_released) { release_h2d_turn_now(h, s.seq + 1); turn_released = true; }
+        return rc;
+    };
+    int rc = upload_batch(s, b, db, true, false);  // the small arrays, on the compute stream
+    if (rc) return fail(rc);
+    {
+        cudaEvent_t e0 = s.events.get(), e1 = s.events.get();
+        cudaEventRecord(e0, cs);
+        for (auto& p : pieces) {
+            if (p.b1 > p.b0 &&
+                cudaMemcpyAsync((u8*)db.arena.p + p.b0, b->arena + p.b0, p.b1 - p.b0, cudaMemcpyHostToDevice, cs) != cudaSuccess) {
+                s.err = "staged arena copy failed";
+                return fail(DGC_E_CUDA);
+            }
+            p.copied = s.events.get();
+            cudaEventRecord(p.copied, cs);
+        }
+        cudaEventRecord(e1, cs);
+        s.spans.push_back({PH_H2D, {e0, e1}});
+        TurnMsg* m = new TurnMsg{h, s.seq + 1};
+        if (cudaLaunchHostFunc(cs, release_h2d_turn_cb, m) == cudaSuccess) turn_released = true;
+        else { delete m; cudaGetLastError(); cudaStreamSynchronize(cs); fail(0); }
+    }
+
+    const size_t T = db.T;
+    s.results = dgc_results{};
+    s.results.n_targets = db.T;
+    s.res_frag_begin.assign(T + 1, 0);
+    s.res_r0.clear(); s.res_r1.clear(); s.res_seq_off.clear(); s.res_seq_len.clear();
+    rc = ensure_alignment_arrays(s, db);
+    if (rc) return rc;
+    for (DevBuf* d : {&s.t_status, &s.t_V, &s.t_E, &s.t_ne, &s.t_nv, &s.t_cons_len, &s.t_nfrag, &s.frag_cap, &s.gs_cap, &s.t_frag_coff,
+                      &s.pool_cap, &s.t_pool_top})
+        CU(d->ensure(4 * (T + 1)));
+    for (DevBuf* d : {&s.t_cols, &s.t_cons_coff, &s.rec_off, &s.pos_off, &s.cons_off, &s.frag_off, &s.gs_off})
+        CU(d->ensure(8 * (T + 1)));
+    CU(s.totals.ensure(64));
+    CU(s.hp_plan_in.ensure(20 * (T + 1) + 16));
+    CU(s.hp_plan_out.ensure(64 * (T + 1)));
+    CU(cudaMemsetAsync(s.totals.p, 0, 64, st));
+    CU(cudaMemsetAsync(s.t_cons_len.p, 0, 4 * (T + 1), st));
+    CU(cudaMemsetAsync(s.t_nfrag.p, 0, 4 * (T + 1), st));
+
+    uint32_t* hp_status = s.hp_plan_in.as<uint32_t>();
+    uint32_t* hp_V = hp_status + (T + 1);
+    uint32_t* hp_E = hp_V + (T + 1);
+    uint64_t* hp_cols = (uint64_t*)(hp_E + (T + 1) + ((T + 1) & 1));
+    uint64_t* p_rec = s.hp_plan_out.as<uint64_t>();
+    uint64_t* p_pos = p_rec + (T + 1);
+    uint64_t* p_cons = p_pos + (T + 1);
+    uint64_t* p_frag = p_cons + (T + 1);
+    uint64_t* p_gs = p_frag + (T + 1);
+    uint32_t* p_fcap = (uint32_t*)(p_gs + (T + 1));
+    uint32_t* p_gcap = p_fcap + (T + 1);
+    uint32_t* p_pcap = p_gcap + (T + 1);
+    const uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
+
+    Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t built_to = 0, planned_to = 0, pend_maxL2 = 0, nchunks = 0;
+    uint64_t out_cons_need = 0, out_frag_need = 0, live_cons = 0, live_frag = 0, raw_seen = 0;
+
+    // does chunk c fit the arenas as they are allocated now?
+    auto cap_ok = [&](const Chunk& c) {
+        return 128 * c.nUnits + 256 <= s.rec.cap && c.nCons + 64 <= s.cons.cap && 8 * c.nFrag + 64 <= s.frags.cap &&
+               4 * c.nGs + 64 <= s.gscratch.cap && (9ull * c.maxL2 <= h->build_smem_max || 9 * c.nPos + 64 <= s.gacc.cap);
+    };
+    // (re)allocate the chunk arenas for c; only while no chunk is open (cudaFree waits for the kernels still using them)
+    auto cap_ensure = [&](const Chunk& c) -> int {
+        CU(s.rec.ensure(128 * c.nUnits + 256));
+        CU(s.cons.ensure(c.nCons + 64)); CU(s.frags.ensure(8 * c.nFrag + 64)); CU(s.gscratch.ensure(4 * c.nGs + 64));
+        if (9ull * c.maxL2 > h->build_smem_max) CU(s.gacc.ensure(9 * c.nPos + 64));
+        return DGC_OK;
+    };
+    auto flush_build = [&]() -> int {
+        if (built_to == planned_to) return DGC_OK;
+        const size_t a = built_to, n = planned_to - built_to;
+        PullArgs pa;
+        const uint32_t nn = (uint32_t)n;
+        pa.dst[0] = (u32*)(s.rec_off.as<u64>() + a); pa.src[0] = (const u32*)(p_rec + a); pa.words[0] = 2 * nn;
+        pa.dst[1] = (u32*)(s.pos_off.as<u64>() + a); pa.src[1] = (const u32*)(p_pos + a); pa.words[1] = 2 * nn;
+        pa.dst[2] = (u32*)(s.cons_off.as<u64>() + a); pa.src[2] = (const u32*)(p_cons + a); pa.words[2] = 2 * nn;
+        pa.dst[3] = (u32*)(s.frag_off.as<u64>() + a); pa.src[3] = (const u32*)(p_frag + a); pa.words[3] = 2 * nn;
+        pa.dst[4] = (u32*)(s.gs_off.as<u64>() + a); pa.src[4] = (const u32*)(p_gs + a); pa.words[4] = 2 * nn;
+        pa.dst[5] = s.frag_cap.as<u32>() + a; pa.src[5] = p_fcap + a; pa.words[5] = nn;
+        pa.dst[6] = s.gs_cap.as<u32>() + a; pa.src[6] = p_gcap + a; pa.words[6] = nn;
+        pa.dst[7] = s.pool_cap.as<u32>() + a; pa.src[7] = p_pcap + a; pa.words[7] = nn;
+        k_pull_words<<<16, 256, 0, st>>>(pa);  // not a memcpy: see k_pull_words
+        s.tm.launches++;
+        CU(cudaGetLastError());
+        const int r = launch_build(s, db, built_to, planned_to - built_to, pend_maxL2);
+        built_to = planned_to; pend_maxL2 = 0;
+        return r;
+    };
+    auto close_chunk = [&]() -> int {
+        int r = flush_build();
+        if (r || !cur.count) return r;
+        CU(s.out_cons.ensure_keep(out_cons_need + 64, live_cons));
+        CU(s.out_frags.ensure_keep(8 * out_frag_need + 64, 8 * live_frag));
+        live_cons = out_cons_need; live_frag = out_frag_need;
+        r = launch_serial(s, db, cur, 2);
+        s.tm.arena_bytes += chunk_bytes(cur);
+        nchunks++;
+        cur = Chunk{cur.first + cur.count, 0, 0, 0, 0, 0, 0, 0};
+        return r;
+    };
+
+    std::vector<Chunk> need;  // per target of the current piece: what it adds to a chunk
+    Chunk total{0, 0, 0, 0, 0, 0, 0, 0};
+    for (size_t pi = 0; pi < pieces.size(); pi++) {
+        const Piece& p = pieces[pi];
+        const size_t t0 = p.t0, nT = p.t1 - p.t0;
+        CU(cudaStreamWaitEvent(st, p.copied, 0));
+        span_begin(s, PH_NORM);
+        rc = launch_normalize(s, db, p.k0, p.k1);
+        if (rc) return rc;
+        span_end(s);
+        span_begin(s, PH_COUNT);
+        rc = launch_plan(s, db, p.t0, p.t1);
+        if (rc) return rc;
+        span_end(s);
+        CU(cudaMemcpyAsync(hp_status + t0, s.t_status.as<u32>() + t0, 4 * nT, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(hp_V + t0, s.t_V.as<u32>() + t0, 4 * nT, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(hp_E + t0, s.t_E.as<u32>() + t0, 4 * nT, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(hp_cols + t0, s.t_cols.as<u64>() + t0, 8 * nT, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+
+        // ---- what every target of the piece needs (same sizing rules as run_pipeline)
+        need.assign(nT, Chunk{0, 1, 0, 0, 0, 0, 0, 0});
+        Chunk sum{0, 0, 0, 0, 0, 0, 0, 0};
+        uint64_t piece_cons = 0, piece_frag = 0;
+        for (size_t i = 0; i < nT; i++) {
+            const size_t t = t0 + i;
+            const bool ok = hp_status[t] == T_OK;
+            const uint64_t V = ok ? hp_V[t] : 0, E = ok ? hp_E[t] : 0, L2 = ok ? (uint64_t)db.h_tlen[t] + 2 : 0;
+            const uint32_t A = db.h_aln_begin[t + 1] - db.h_aln_begin[t];
+            const uint64_t pcap = ok ? (4ull * (A + 8) + E / 2 + 256 + 15) & ~15ull : 0;
+            const uint64_t units = ok ? L2 + V + pcap / 16 : 0;
+            const uint64_t fcap = ok ? V / ((uint64_t)o.min_len + 1) + 2 : 0, gcap = ok ? 8ull * (A + 2) + 64 : 0;
+            Chunk& n = need[i];
+            n.nUnits = units; n.nPos = L2; n.nCons = (V + 15) & ~15ull; n.nFrag = fcap; n.nGs = gcap; n.maxL2 = (uint32_t)L2;
+            if (16 * units > 0xFFFFFFF0ull) { s.err = "one target's graph exceeds the 32 GiB a list pointer can address"; return DGC_E_NOMEM; }
+            if (chunk_bytes(n) > budget) { s.err = "one target needs more than scratch_bytes of graph arena"; return DGC_E_NOMEM; }
+            p_fcap[t] = (uint32_t)fcap; p_gcap[t] = (uint32_t)gcap; p_pcap[t] = (uint32_t)pcap;
+            sum.nUnits += units; sum.nPos += L2; sum.nCons += n.nCons; sum.nFrag += fcap; sum.nGs += gcap;
+            sum.maxL2 = std::max(sum.maxL2, n.maxL2);
+            piece_cons += V; piece_frag += fcap;
+            s.tm.nodes += V; s.tm.norm_cols += ok ? hp_cols[t] : 0;
+        }
+        total.nUnits += sum.nUnits; total.nPos += sum.nPos; total.nCons += sum.nCons; total.nFrag += sum.nFrag; total.nGs += sum.nGs;
+        uint64_t piece_raw = 0;
+        for (uint32_t k = p.k0; k < p.k1; k++) piece_raw += b->aln_len[k];
+        raw_seen += piece_raw;
+        // ---- with no chunk open the arenas may be (re)allocated: size them for the rest of the batch, scaled from
+        // this piece by raw columns, within the budget
+        if (cur.count == 0) {
+            const double scale = piece_raw ? 1.06 * (double)(db.raw_cols - raw_seen + piece_raw) / (double)piece_raw : 1.0;
+            Chunk est = sum;
+            est.nUnits = (uint64_t)(sum.nUnits * scale); est.nPos = (uint64_t)(sum.nPos * scale); est.nCons = (uint64_t)(sum.nCons * scale);
+            est.nFrag = (uint64_t)(sum.nFrag * scale); est.nGs = (uint64_t)(sum.nGs * scale);
+            if (chunk_bytes(est) > budget) {
+                const double f = (double)budget / (double)chunk_bytes(est);
+                est.nUnits = (uint64_t)(est.nUnits * f); est.nPos = (uint64_t)(est.nPos * f); est.nCons = (uint64_t)(est.nCons * f);
+                est.nFrag = (uint64_t)(est.nFrag * f); est.nGs = (uint64_t)(est.nGs * f);
+            }
+            if (pi == 0) {  // an estimate that fell short last time costs a second sweep: remember what a whole batch took
+                Chunk hx = est;
+                hx.nUnits = std::max(est.nUnits, s.hint[0]); hx.nPos = std::max(est.nPos, s.hint[1]); hx.nCons = std::max(est.nCons, s.hint[2]);
+                hx.nFrag = std::max(est.nFrag, s.hint[3]); hx.nGs = std::max(est.nGs, s.hint[4]);
+                if (chunk_bytes(hx) <= budget) est = hx;
+            }
+            if (!cap_ok(est) && (rc = cap_ensure(est)) != DGC_OK) {  // cannot have it all: fall back to what this piece needs
+                cudaGetLastError();
+                s.err.clear();
+            }
+            const uint64_t oc = (uint64_t)((out_cons_need + piece_cons) + piece_cons * (scale - 1.0));
+            const uint64_t of = (uint64_t)((out_frag_need + piece_frag) + piece_frag * (scale - 1.0));
+            CU(s.out_cons.ensure_keep(oc + 64, live_cons));
+            CU(s.out_frags.ensure_keep(8 * of + 64, 8 * live_frag));
+        }
+        // ---- arena offsets target by target; a chunk closes when the next target does not fit
+        for (size_t i = 0; i < nT; i++) {
+            const size_t t = t0 + i;
+            const Chunk& n = need[i];
+            Chunk nxt = cur;
+            nxt.nUnits += n.nUnits; nxt.nPos += n.nPos; nxt.nCons += n.nCons; nxt.nFrag += n.nFrag; nxt.nGs += n.nGs; nxt.count++;
+            nxt.maxL2 = std::max(cur.maxL2, n.maxL2);
+            if (cur.count && (chunk_bytes(nxt) > budget || !cap_ok(nxt) || cur.count >= (1u << 20))) {
+                if ((rc = close_chunk()) != DGC_OK) return rc;
+                nxt = n; nxt.first = (uint32_t)t; nxt.count = 1;
+            }
+            if (cur.count == 0) {
+                cur.first = (uint32_t)t;
+                if (!cap_ok(nxt)) {  // an empty chunk that still does not fit: grow to the rest of this piece (or this target)
+                    Chunk rest{0, 0, 0, 0, 0, 0, 0, 0};
+                    for (size_t j = i; j < nT; j++) {
+                        rest.nUnits += need[j].nUnits; rest.nPos += need[j].nPos; rest.nCons += need[j].nCons;
+                        rest.nFrag += need[j].nFrag; rest.nGs += need[j].nGs; rest.maxL2 = std::max(rest.maxL2, need[j].maxL2);
+                    }
+                    if (chunk_bytes(rest) > budget || cap_ensure(rest) != DGC_OK) {
+                        cudaGetLastError();
+                        s.err.clear();
+                        if ((rc = cap_ensure(nxt)) != DGC_OK) return rc;
+                    }
+                }
+            }
+            p_rec[t] = cur.nUnits; p_pos[t] = cur.nPos; p_cons[t] = cur.nCons; p_frag[t] = cur.nFrag; p_gs[t] = cur.nGs;
+            cur.nUnits += n.nUnits; cur.nPos += n.nPos; cur.nCons += n.nCons; cur.nFrag += n.nFrag; cur.nGs += n.nGs; cur.count++;
+            cur.maxL2 = std::max(cur.maxL2, n.maxL2);
+            pend_maxL2 = std::max(pend_maxL2, n.maxL2);
+            out_cons_need += hp_status[t] == T_OK ? hp_V[t] : 0; out_frag_need += n.nFrag;
+            planned_to = (uint32_t)t + 1;
+        }
+        if ((rc = flush_build()) != DGC_OK) return rc;
+    }
+    if ((rc = close_chunk()) != DGC_OK) return rc;
+    s.tm.chunks = nchunks;
+    if (chunk_bytes(total) <= budget) {
+        const uint64_t add = 1024;
+        s.hint[0] = total.nUnits + add; s.hint[1] = total.nPos + add; s.hint[2] = total.nCons + add; s.hint[3] = total.nFrag + add;
+        s.hint[4] = total.nGs + add;
+    }
+    return fetch_results(s, db);
 }
 
 void finish_timings(Slot& s) {
@@ -498,8 +855,23 @@ void begin_run(Slot& s) {
 
 int slot_process(Slot& s, const dgc_batch* b) {
     begin_run(s);
-    int rc = upload_batch(s, b, s.db, true);
-    if (rc == DGC_OK) rc = run_pipeline(s, s.db, 2, 0xFFFFFFFFu);
+    dgc_handle* h = s.h;
+    {
+        std::unique_lock<std::mutex> lk(h->h2d_mu);
+        h->h2d_cv.wait(lk, [&] { return h->h2d_turn == s.seq; });
+    }
+    int rc;
+    std::vector<Piece> pieces;
+    const uint32_t want = b->arena_bytes >= h->stage_min_bytes ? (uint32_t)std::min<uint64_t>(16, b->arena_bytes / h->stage_piece_bytes) : 0;
+    if (split_pieces(b, want, pieces)) {
+        rc = run_staged(s, b, pieces);  // hands the link to the next batch as soon as its own bytes have landed
+    } else {
+        rc = upload_batch(s, b, s.db, true);
+        cudaStreamSynchronize(s.stream);
+        release_h2d_turn_now(h, s.seq + 1);
+        if (rc == DGC_OK) rc = run_pipeline(s, s.db, 2, 0xFFFFFFFFu);
+    }
+    cudaStreamSynchronize(s.copy_stream);
     cudaStreamSynchronize(s.stream);
     finish_timings(s);
     return rc;
@@ -561,6 +933,8 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
     h->opts = *opts;
     h->device = opts->device;
     h->sm_count = prop.multiProcessorCount;
+    if (const char* e1 = getenv("DGC_STAGE_PIECE_BYTES")) h->stage_piece_bytes = std::max<uint64_t>(1, strtoull(e1, nullptr, 10));
+    if (const char* e2 = getenv("DGC_STAGE_MIN_BYTES")) h->stage_min_bytes = strtoull(e2, nullptr, 10);
     {   // opt in to large dynamic shared memory for the build kernel (static use is ~4.2 KB)
         size_t optin = prop.sharedMemPerBlockOptin > 8192 ? prop.sharedMemPerBlockOptin - 8192 : 0;
         optin = std::min<size_t>(optin, 200 * 1024);
@@ -571,7 +945,8 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
     for (int i = 0; i < NSLOT; i++) {
         Slot& s = h->slots[i];
         s.h = h; s.index = i;
-        if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess ||
+            (e = cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking)) != cudaSuccess) {
             g_create_error = cudaGetErrorString(e);
             delete h;
             return DGC_E_CUDA;
@@ -606,6 +981,7 @@ int dgc_destroy(dgc_handle* h) {
             b->release();
         s.events.destroy();
         cudaStreamDestroy(s.stream);
+        if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
     }
     delete h;
     return DGC_OK;
@@ -626,12 +1002,21 @@ int dgc_submit(dgc_handle* h, const dgc_batch* batch) {
     if (!h) return DGC_E_INVALID;
     int rc = validate_batch(batch, h->err);
     if (rc) return rc;
-    if (h->submitted - h->collected >= NSLOT - 1) { h->err = "too many batches in flight: collect first"; return DGC_E_STATE; }
-    Slot& s = h->slots[h->submitted % NSLOT];
+    int si = -1;
+    {
+        std::lock_guard<std::mutex> lk(h->q_mu);
+        if (h->inflight.size() >= (size_t)DGC_MAX_INFLIGHT) { h->err = "too many batches in flight: collect first"; return DGC_E_STATE; }
+        for (int i = 0; i < NSLOT && si < 0; i++)
+            if (!h->busy[i]) si = i;
+        h->busy[si] = true;
+        h->inflight.push_back(si);
+    }
+    Slot& s = h->slots[si];
     {
         std::unique_lock<std::mutex> lk(s.mu);
         s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
         s.pending = *batch;
+        s.seq = h->submitted;
         s.state = Slot::QUEUED;
         s.cv.notify_all();
     }
@@ -641,8 +1026,13 @@ int dgc_submit(dgc_handle* h, const dgc_batch* batch) {
 
 int dgc_collect(dgc_handle* h, dgc_results* out) {
     if (!h || !out) return DGC_E_INVALID;
-    if (h->collected == h->submitted) { h->err = "nothing submitted"; return DGC_E_STATE; }
-    Slot& s = h->slots[h->collected % NSLOT];
+    int si;
+    {
+        std::lock_guard<std::mutex> lk(h->q_mu);
+        if (h->inflight.empty()) { h->err = "nothing submitted"; return DGC_E_STATE; }
+        si = h->inflight.front();
+    }
+    Slot& s = h->slots[si];
     int rc;
     {
         std::unique_lock<std::mutex> lk(s.mu);
@@ -652,6 +1042,11 @@ int dgc_collect(dgc_handle* h, dgc_results* out) {
     }
     h->collected++;
     h->last_tm = s.tm;
+    {   // the slot is free again: its result buffers stay untouched until a later submit takes it
+        std::lock_guard<std::mutex> lk(h->q_mu);
+        h->inflight.pop_front();
+        h->busy[si] = false;
+    }
     if (rc) { h->err = s.err; return rc; }
     *out = s.results;
     return DGC_OK;

@@ -34,6 +34,7 @@ typedef unsigned long long u64;
 #define F_NO_TRIM 2u
 #define F_NO_MERGE 4u
 #define F_SINGLE 8u
+#define F_NO_PREFETCH 256u
 
 __device__ __forceinline__ u32 n_base(u32 bfv) { return bfv & 0xFFu; }
 __device__ __forceinline__ u32 n_flags(u32 bfv) { return (bfv >> 8) & 0xFFu; }
@@ -104,7 +105,8 @@ struct NormArgs {
     const u64* aln_q_off;
     const u64* aln_t_off;
     const u64* aln_norm_off;  // column offset of this alignment's slot in `norm` (capacity 2*len)
-    u32 n_alns, min_len, trim, flags;
+    u32 n_alns, min_len, trim, flags;  // n_alns: end of the alignment range
+    u32 aln_first;                     // start of the alignment range (staged uploads run one piece at a time)
     u32 retry_only;  // serial kernel: handle only the alignments the warp kernel flagged AF_RETRY
     u16* norm;  // q | t << 8 per column
     u64* o_off;
@@ -117,7 +119,7 @@ struct NormArgs {
 };
 
 __global__ void __launch_bounds__(128) k_normalize_trim(NormArgs a) {
-    u32 ai = blockIdx.x * blockDim.x + threadIdx.x;
+    u32 ai = a.aln_first + blockIdx.x * blockDim.x + threadIdx.x;
     if (ai >= a.n_alns) return;
     if (a.retry_only && a.o_flags[ai] != 2u /* AF_RETRY */) return;
     const u64 n = a.aln_len[ai];
@@ -197,7 +199,8 @@ __global__ void __launch_bounds__(128) k_normalize_trim(NormArgs a) {
 // K1b: per target, the min-coverage filter (main.cpp:66-72,118), alignment validation, and the
 // exact vertex count / edge bound that size the arena.
 struct PlanArgs {
-    u32 n_targets, min_cov;
+    u32 n_targets, min_cov;  // n_targets: end of the target range
+    u32 t_first;             // start of the target range
     const u32* tgt_tlen;
     const u32* tgt_aln_begin;
     const u32* a_start;
@@ -212,7 +215,7 @@ struct PlanArgs {
     u64* tgt_cols;
 };
 __global__ void k_target_plan(PlanArgs a) {
-    u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+    u32 t = a.t_first + blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= a.n_targets) return;
     u32 a0 = a.tgt_aln_begin[t], a1 = a.tgt_aln_begin[t + 1], A = a1 - a0, L = a.tgt_tlen[t];
     u32 st = T_OK;
@@ -264,6 +267,20 @@ __device__ __forceinline__ void block_scan2(u32 vs, u32 vm, u32& ex_s, u32& ex_m
     tot_s = ts;
     tot_m = tm;
     __syncthreads();
+}
+
+// Staged uploads: the planner's per-target offsets live in pinned (device-visible) host memory.  They are pulled by
+// a kernel instead of cudaMemcpyAsync because an H2D memcpy would queue on the copy engine BEHIND the gigabytes of
+// alignment strings still travelling on the copy stream, and the build of the first piece would wait for all of them.
+struct PullArgs {
+    u32* dst[8];
+    const u32* src[8];
+    u32 words[8];
+};
+__global__ void __launch_bounds__(256) k_pull_words(PullArgs a) {
+#pragma unroll 1
+    for (int j = 0; j < 8; j++)
+        for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < a.words[j]; i += gridDim.x * blockDim.x) a.dst[j][i] = a.src[j][i];
 }
 
 #include "graph_rec.cuh"

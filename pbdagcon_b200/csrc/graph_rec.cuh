@@ -55,7 +55,22 @@ struct GV {           // one target's graph
     u32 nbb;          // L + 2
     u32 pool_top, pool_end;  // 8-byte word indices from base
     u32 status;
+    u32 nunits;       // record units in front of the pool: handles are < nunits; 0 switches the prefetches off
 };
+
+// The two sweeps (mergeNodes forwards, bestPath backwards) are chains of dependent loads: a vertex is first seen as
+// a neighbour's slot (header needed at once), popped a step or two later (its own slots needed), and its neighbours'
+// headers after that.  Each of those was a separate DRAM miss (ncu r01b: 45 % of the stall samples on three loads).
+// So whenever a lane first touches a vertex it asks L2 for the whole record and, once the record's first slots have
+// arrived, for the records those slots name: the chain then runs one step behind its own prefetches.
+__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void gv_prefetch_rec(const GV& g, u32 h) {
+    if (h < g.nunits) {  // a slot past a list's length holds stale bytes: never form an address outside the arena
+        const u8* r = g.base + (size_t)h * REC_UNIT;
+        pf_l2(r);
+        pf_l2(r + 64);
+    }
+}
 
 __device__ __forceinline__ Hdr* gb_hdr(u8* base, u32 h) { return (Hdr*)(base + (size_t)h * REC_UNIT); }
 __device__ __forceinline__ OSlot* gb_out(u8* base, u32 out_ptr) { return (OSlot*)(base + (size_t)out_ptr * 8); }
@@ -674,15 +689,23 @@ __device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx&
     c.g.pool_top = a.tgt_pool_top[t];
     c.g.pool_end = pool_begin + a.pool_cap[t];
     c.g.status = T_OK;
+    c.g.nunits = (a.flags & F_NO_PREFETCH) ? 0u : pool_begin / 16u;
     c.S = a.gscratch + a.gscratch_off[t];
     c.scap = a.gscratch_cap[t];
     return true;
 }
 
+#ifndef WARP_KERNEL_THREADS
 #define WARP_KERNEL_THREADS 128
+#endif
+#ifndef MERGE_MIN_BLOCKS
+#define MERGE_MIN_BLOCKS 10  // resident 128-thread blocks per SM k_merge_nodes2's register allocation must allow: 48 registers,
+                             // 40 warps per SM.  Measured on B200 (10 000 targets): 8 blocks 168 ms, 9-10 blocks 133-135 ms, 12 blocks
+                             // (40 registers, spills) 143 ms, 16 blocks 161 ms
+#endif
 
 // mergeNodes :129-160
-__global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_merge_nodes2(Serial2Args a) {
+__global__ void __launch_bounds__(WARP_KERNEL_THREADS, MERGE_MIN_BLOCKS) k_merge_nodes2(Serial2Args a) {
     u32 t;
     T2Ctx c;
     if (!warp2_setup(a, t, c)) return;
@@ -747,7 +770,15 @@ __global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_merge_nodes2(Serial2Arg
         OSlot sl;
         sl.dst = 0; sl.cv = 0;
         uint2 d = make_uint2(0u, 0u);
-        if (have) { sl = gv_out(g, hu.out_ptr)[lane]; d = *(const uint2*)gv_hdr(g, sl.dst); }
+        if (have) {
+            sl = gv_out(g, hu.out_ptr)[lane];
+            const u8* rv = g.base + (size_t)sl.dst * REC_UNIT;
+            d = *(const uint2*)rv;
+            const uint4 o01 = *(const uint4*)(rv + REC_OUT_OFF);  // the successor's first two out-slots (inline position)
+            if (g.nunits) pf_l2(rv + 32);
+            if (d.y >> 16) gv_prefetch_rec(g, o01.x);
+            if ((d.y >> 16) > 1) gv_prefetch_rec(g, o01.z);
+        }
         {
             const bool cand = have && (d.y & 0xFFFFu) == 1;
             const u32 key = d.x & 0xFFu;
@@ -940,10 +971,15 @@ __global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_best_path2(Serial2Args 
             if (have) {
                 s = gv_in(g, hn.in_ptr)[b0 + lane];
                 Hdr* hs = gv_hdr(g, s);
+                const u32 sdeg = hs->deg;
                 const u32 k = (u32)(hs->cnt + 1);
+                const uint2 i01 = *(const uint2*)((const u8*)hs + REC_IN_OFF);  // the predecessor's first two in-slots (inline position)
+                if (g.nunits) pf_l2((const u8*)hs + 64);                        // its out-slots, for when it is popped
                 hs->cnt = (int)k;
-                ready = k == (hs->deg >> 16);
+                ready = k == (sdeg >> 16);
                 if (ready) hs->best = NIL;
+                if (sdeg & 0xFFFFu) gv_prefetch_rec(g, i01.x);
+                if ((sdeg & 0xFFFFu) > 1) gv_prefetch_rec(g, i01.y);
             }
             __syncwarp();
             m2_queue_append(g, __ballot_sync(FULLMASK, ready), ready, s, tail, lane);

@@ -119,7 +119,7 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, u32 lane) {
 __global__ void __launch_bounds__(NW_WARPS * 32, 2) k_normalize_warp(NormArgs a) {
     __shared__ NwSmem sm_all[NW_WARPS];
     const u32 lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const u32 ai = blockIdx.x * NW_WARPS + wid;
+    const u32 ai = a.aln_first + blockIdx.x * NW_WARPS + wid;
     if (ai >= a.n_alns) return;
     NwSmem& sm = sm_all[wid];
     const u32 n = a.aln_len[ai];
