@@ -293,6 +293,8 @@ def run_gpu(args):
 
     if RANK != 0:
         eng.close()
+        if WORLD > 1:
+            dist.destroy_process_group()
         return
 
     # ---- roofline of the dominant kernel (HBM-bound integer/byte work; no tensor cores on this path)
@@ -305,6 +307,8 @@ def run_gpu(args):
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     kern = {"normalize_trim": phases.get("ms_normalize", 0), "build_graph": phases.get("ms_build", 0),
             "merge_nodes": phases.get("ms_merge", 0), "best_path": phases.get("ms_bestpath", 0)}
+    if kern["best_path"] == 0:      # default: both sweeps run as one launch (k_merge_best2); --flags 512 splits them
+        kern = {"normalize_trim": kern["normalize_trim"], "build_graph": kern["build_graph"], "merge_best": kern["merge_nodes"]}
     top = max(kern, key=kern.get)
     n_launch_top = args.steps * max(1, tm["chunks"]) if top != "normalize_trim" else args.steps
     alg_bytes_step = alg_in + frag_bytes                 # B_alg summed over the batch
@@ -345,6 +349,8 @@ def run_gpu(args):
                     "targets_per_s": tot_targets * args.steps / e2e_s, "ms_per_step": e2e_s * 1e3 / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
+    if WORLD > 1:
+        dist.destroy_process_group()
 
 
 def main():

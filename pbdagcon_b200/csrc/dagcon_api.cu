@@ -340,6 +340,13 @@ int launch_serial(Slot& s, dgc_dbatch& db, const Chunk& c, int stop_after) {
     sa.frag_cap = s.frag_cap.as<u32>(); sa.tgt_cons_len = s.t_cons_len.as<u32>(); sa.tgt_nfrag = s.t_nfrag.as<u32>();
     const uint32_t warps_per_block = WARP_KERNEL_THREADS / 32;   // one warp per target
     const uint32_t grid = (c.count + warps_per_block - 1) / warps_per_block;
+    if (stop_after >= 2 && !(o.flags & (DGC_F_NO_MERGE | DGC_F_SPLIT_SWEEPS))) {
+        span_begin(s, PH_MERGE);  // both sweeps in one launch; reported as ms_merge
+        k_merge_best2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
+        s.tm.launches++;
+        CU(cudaGetLastError());
+        span_end(s);
+    } else {
     if (!(o.flags & DGC_F_NO_MERGE)) {
         span_begin(s, PH_MERGE);
         k_merge_nodes2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
@@ -353,6 +360,7 @@ int launch_serial(Slot& s, dgc_dbatch& db, const Chunk& c, int stop_after) {
     s.tm.launches++;
     CU(cudaGetLastError());
     span_end(s);
+    }
     span_begin(s, PH_COMPACT);
     // scan over the chunk's targets, chained through `totals` so chunks append to one output
     k_scan_outputs<<<1, 1024, 0, st>>>(c.count, s.t_status.as<u32>() + c.first, s.t_cons_len.as<u32>() + c.first,

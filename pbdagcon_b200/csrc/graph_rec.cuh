@@ -705,10 +705,7 @@ __device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx&
 #endif
 
 // mergeNodes :129-160
-__global__ void __launch_bounds__(WARP_KERNEL_THREADS, MERGE_MIN_BLOCKS) k_merge_nodes2(Serial2Args a) {
-    u32 t;
-    T2Ctx c;
-    if (!warp2_setup(a, t, c)) return;
+__device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2Ctx& c) {
     GV& g = c.g;
     const u32 lane = threadIdx.x & 31;
     const u32 ENTER = 0;
@@ -914,6 +911,14 @@ __global__ void __launch_bounds__(WARP_KERNEL_THREADS, MERGE_MIN_BLOCKS) k_merge
         if (status == T_OK) status = g.status;
         if (status != T_OK) a.tgt_status[t] = status;
     }
+    __syncwarp();
+    return __shfl_sync(FULLMASK, status, 0);
+}
+__global__ void __launch_bounds__(WARP_KERNEL_THREADS, MERGE_MIN_BLOCKS) k_merge_nodes2(Serial2Args a) {
+    u32 t;
+    T2Ctx c;
+    if (!warp2_setup(a, t, c)) return;
+    merge_sweep(a, t, c);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -926,10 +931,7 @@ __device__ __forceinline__ u32 f2ord(float f) {  // order-preserving map float -
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-__global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_best_path2(Serial2Args a) {
-    u32 t;
-    T2Ctx c;
-    if (!warp2_setup(a, t, c)) return;
+__device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, const T2Ctx& c) {
     const GV& g = c.g;
     const u32 lane = threadIdx.x & 31;
     const u32 L = a.tgt_tlen[t], ENTER = 0, EXIT = 2 * (L + 1), nV = a.tgt_nv[t];
@@ -1035,4 +1037,21 @@ __global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_best_path2(Serial2Args 
     a.tgt_cons_len[t] = (u32)idx;
     a.tgt_nfrag[t] = nfrag;
     if (status != T_OK) { a.tgt_status[t] = status; a.tgt_nfrag[t] = 0; }
+}
+__global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_best_path2(Serial2Args a) {
+    u32 t;
+    T2Ctx c;
+    if (!warp2_setup(a, t, c)) return;
+    best_sweep(a, t, c);
+}
+
+// K3 + K4 in one launch: a warp that has merged its target goes straight on to the best path.  The reverse sweep
+// starts at exit, where the forward sweep has just ended (those records are still in L2), and the warps that finish
+// mergeNodes early no longer wait at a kernel boundary for the longest chain of the launch.
+__global__ void __launch_bounds__(WARP_KERNEL_THREADS, MERGE_MIN_BLOCKS) k_merge_best2(Serial2Args a) {
+    u32 t;
+    T2Ctx c;
+    if (!warp2_setup(a, t, c)) return;
+    if (merge_sweep(a, t, c) != T_OK) return;
+    best_sweep(a, t, c);
 }
