@@ -297,6 +297,22 @@ int launch_plan(Slot& s, const dgc_dbatch& db, uint32_t t0, uint32_t t1) {
 }
 
 struct Chunk { uint32_t first, count; uint64_t nUnits, nPos, nCons, nFrag, nGs; uint32_t maxL2; };
+uint64_t chunk_bytes(const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; }
+
+// Pool of list blocks behind a target's records, in 8-byte words (a multiple of 16 keeps every arena 128-byte
+// aligned): enter's out-list and exit's in-list always, the rest only when a list outgrows its record.  The normal
+// size covers the coverages the record layout was shaped for; `worst` is the bound for the rebuild of a target whose
+// pool ran dry (T_POOL): lists double when they grow, so a backbone in-list costs <= 2 words and a backbone
+// out-list <= 4 words per edge that can reach a backbone vertex (Bin = sum of nE - nI over the alignments), and the
+// merges re-home at most a few slots per edge.
+bool g_tiny_pool = false;  // DGC_TEST_TINY_POOL: first-pass pools hold the enter/exit lists only, so that the tests reach the rebuild
+uint64_t pool_words(uint64_t V, uint64_t E, uint64_t L, uint32_t A, bool worst) {
+    if (!worst && g_tiny_pool) return (4ull * (A + 8) + 15) & ~15ull;
+    if (!worst) return (4ull * (A + 8) + E / 2 + 256 + 15) & ~15ull;
+    const uint64_t sE = E > L + 1 + A + 16 ? E - (L + 1) - A - 16 : 0, sI = V > L + 2 ? V - (L + 2) : 0;
+    const uint64_t bin = sE > sI ? sE - sI : 0;
+    return (4ull * (A + 8) + 256 + 2 * bin + 4 * (bin + A) + 8 * E + 15) & ~15ull;
+}
 
 // K2 for targets [first, first + count) of the current chunk (their arena offsets are on the device already)
 int launch_build(Slot& s, dgc_dbatch& db, uint32_t first, uint32_t count, uint32_t maxL2) {
@@ -398,7 +414,9 @@ int fetch_results(Slot& s, dgc_dbatch& db) {
     CU(cudaStreamSynchronize(st));
 
     // ---- CnsResult records in target order
-    const uint32_t* rs = s.r_status.as<uint32_t>();
+    uint32_t* rs = s.r_status.as<uint32_t>();
+    for (size_t t = 0; t < T; t++)
+        if (rs[t] == T_POOL) rs[t] = T_INTERNAL;  // not even the worst-case pool was enough (or addressable)
     const uint64_t* cc = s.r_cons_coff.as<uint64_t>();
     const uint32_t* fc = s.r_frag_coff.as<uint32_t>();
     const int32_t* fr = s.r_frags.as<int32_t>();
@@ -425,6 +443,70 @@ int fetch_results(Slot& s, dgc_dbatch& db) {
     return DGC_OK;
 }
 
+
+// Second pass for the targets whose list pool ran dry (status T_POOL after the sweeps of their chunk): each run of
+// such targets is planned again with the worst-case pool, rebuilt and swept.  By now the arenas hold nothing that is
+// still needed (every chunk's results have been compacted), so they may be re-allocated.  hp_V / hp_E / the p_* offset
+// arrays are the pinned planner arrays of this run.
+int retry_pool_failures(Slot& s, dgc_dbatch& db, int stop_after) {
+    dgc_handle* h = s.h;
+    const dgc_opts& o = h->opts;
+    const size_t T = db.T;
+    cudaStream_t st = s.stream;
+    uint32_t* hp_status = s.hp_plan_in.as<uint32_t>();
+    const uint32_t* hp_V = hp_status + (T + 1);
+    const uint32_t* hp_E = hp_V + (T + 1);
+    uint64_t* p_rec = s.hp_plan_out.as<uint64_t>();
+    uint64_t* p_pos = p_rec + (T + 1);
+    uint64_t* p_cons = p_pos + (T + 1);
+    uint64_t* p_frag = p_cons + (T + 1);
+    uint64_t* p_gs = p_frag + (T + 1);
+    uint32_t* p_fcap = (uint32_t*)(p_gs + (T + 1));
+    uint32_t* p_gcap = p_fcap + (T + 1);
+    uint32_t* p_pcap = p_gcap + (T + 1);
+    CU(cudaMemcpyAsync(hp_status, s.t_status.p, 4 * T, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
+    size_t t = 0;
+    while (t < T) {
+        if (hp_status[t] != T_POOL) { t++; continue; }
+        // one chunk: the longest run of failed targets from t that fits the budget
+        Chunk c{(uint32_t)t, 0, 0, 0, 0, 0, 0, 0};
+        while (t < T && hp_status[t] == T_POOL) {
+            const uint64_t V = hp_V[t], E = hp_E[t], L2 = (uint64_t)db.h_tlen[t] + 2;
+            const uint32_t A = db.h_aln_begin[t + 1] - db.h_aln_begin[t];
+            const uint64_t pcap = pool_words(V, E, db.h_tlen[t], A, true);
+            const uint64_t units = L2 + V + pcap / 16;
+            if (16 * units > 0xFFFFFFF0ull || pcap > 0xFFFFFFF0ull) break;  // stays T_POOL -> reported as DGC_T_INTERNAL
+            Chunk nxt = c;
+            nxt.nUnits += units; nxt.nPos += L2; nxt.nCons += (V + 15) & ~15ull; nxt.nFrag += p_fcap[t]; nxt.nGs += p_gcap[t]; nxt.count++;
+            if (chunk_bytes(nxt) > budget) break;
+            p_rec[t] = c.nUnits; p_pos[t] = c.nPos; p_cons[t] = c.nCons; p_frag[t] = c.nFrag; p_gs[t] = c.nGs;
+            p_pcap[t] = (uint32_t)pcap;
+            nxt.maxL2 = std::max(c.maxL2, (uint32_t)L2);
+            c = nxt;
+            t++;
+        }
+        if (c.count == 0) { t++; continue; }  // a single target beyond the budget or the 32 GiB a list pointer can address
+        const size_t a = c.first, n = c.count;
+        CU(s.rec.ensure(128 * c.nUnits + 256));
+        CU(s.cons.ensure(c.nCons + 64)); CU(s.frags.ensure(8 * c.nFrag + 64)); CU(s.gscratch.ensure(4 * c.nGs + 64));
+        if (9ull * c.maxL2 > h->build_smem_max) CU(s.gacc.ensure(9 * c.nPos + 64));
+        CU(cudaMemcpyAsync(s.rec_off.as<u64>() + a, p_rec + a, 8 * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.pos_off.as<u64>() + a, p_pos + a, 8 * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.cons_off.as<u64>() + a, p_cons + a, 8 * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.frag_off.as<u64>() + a, p_frag + a, 8 * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.gs_off.as<u64>() + a, p_gs + a, 8 * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.pool_cap.as<u32>() + a, p_pcap + a, 4 * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(s.t_status.as<u32>() + a, 0, 4 * n, st));  // T_OK
+        int rc = launch_build(s, db, c.first, c.count, c.maxL2);
+        if (rc == DGC_OK && stop_after >= 1) rc = launch_serial(s, db, c, stop_after);
+        if (rc) return rc;
+        s.tm.arena_bytes += chunk_bytes(c);
+        s.tm.chunks++;
+    }
+    return DGC_OK;
+}
 
 // The whole hot path for a resident batch.  stop_after: 0 build, 1 merge, 2 everything.
 int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) {
@@ -483,16 +565,13 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
     std::vector<Chunk> chunks;
     Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
-    auto chunk_bytes = [](const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; };
     uint64_t out_cons_cap = 0, out_frag_cap = 0;
     for (size_t t = 0; t < T; t++) {
         const bool ok = hp_status[t] == T_OK && (only_target == 0xFFFFFFFFu || only_target == t);
         if (!ok && hp_status[t] == T_OK) hp_status[t] = T_SKIPPED;  // debug single-target run
         const uint64_t V = ok ? hp_V[t] : 0, E = ok ? hp_E[t] : 0, L2 = ok ? (uint64_t)db.h_tlen[t] + 2 : 0;
         const uint32_t A = db.h_aln_begin[t + 1] - db.h_aln_begin[t];
-        // pool of list blocks behind the records: enter's out-list and exit's in-list always, the rest only when a
-        // list outgrows its record; a multiple of 16 words keeps every target's arena 128-byte aligned
-        const uint64_t pcap = ok ? (4ull * (A + 8) + E / 2 + 256 + 15) & ~15ull : 0;
+        const uint64_t pcap = ok ? pool_words(V, E, db.h_tlen[t], A, false) : 0;
         const uint64_t units = ok ? L2 + V + pcap / 16 : 0;  // backbone records take two units
         const uint64_t fcap = ok ? V / ((uint64_t)o.min_len + 1) + 2 : 0, gcap = ok ? 8ull * (A + 2) + 64 : 0;
         const uint64_t consb = (V + 15) & ~15ull;
@@ -546,6 +625,8 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         rc = launch_serial(s, db, c, stop_after);
         if (rc) return rc;
     }
+    rc = retry_pool_failures(s, db, stop_after);
+    if (rc) return rc;
     if (stop_after < 2) { CU(cudaStreamSynchronize(st)); return DGC_OK; }
     return fetch_results(s, db);
 }
@@ -607,7 +688,6 @@ bool split_pieces(const dgc_batch* b, uint32_t want, std::vector<Piece>& out) {
     return out.size() >= 2;
 }
 
-uint64_t chunk_bytes(const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; }
 
 int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
     dgc_handle* h = s.h;
@@ -751,7 +831,7 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
             const bool ok = hp_status[t] == T_OK;
             const uint64_t V = ok ? hp_V[t] : 0, E = ok ? hp_E[t] : 0, L2 = ok ? (uint64_t)db.h_tlen[t] + 2 : 0;
             const uint32_t A = db.h_aln_begin[t + 1] - db.h_aln_begin[t];
-            const uint64_t pcap = ok ? (4ull * (A + 8) + E / 2 + 256 + 15) & ~15ull : 0;
+            const uint64_t pcap = ok ? pool_words(V, E, db.h_tlen[t], A, false) : 0;
             const uint64_t units = ok ? L2 + V + pcap / 16 : 0;
             const uint64_t fcap = ok ? V / ((uint64_t)o.min_len + 1) + 2 : 0, gcap = ok ? 8ull * (A + 2) + 64 : 0;
             Chunk& n = need[i];
@@ -837,6 +917,7 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
         s.hint[0] = total.nUnits + add; s.hint[1] = total.nPos + add; s.hint[2] = total.nCons + add; s.hint[3] = total.nFrag + add;
         s.hint[4] = total.nGs + add;
     }
+    if ((rc = retry_pool_failures(s, db, 2)) != DGC_OK) return rc;
     return fetch_results(s, db);
 }
 
@@ -942,6 +1023,7 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
     h->device = opts->device;
     h->sm_count = prop.multiProcessorCount;
     if (const char* e1 = getenv("DGC_STAGE_PIECE_BYTES")) h->stage_piece_bytes = std::max<uint64_t>(1, strtoull(e1, nullptr, 10));
+    if (const char* e3 = getenv("DGC_TEST_TINY_POOL")) g_tiny_pool = e3[0] == '1';
     if (const char* e2 = getenv("DGC_STAGE_MIN_BYTES")) h->stage_min_bytes = strtoull(e2, nullptr, 10);
     {   // opt in to large dynamic shared memory for the build kernel (static use is ~4.2 KB)
         size_t optin = prop.sharedMemPerBlockOptin > 8192 ? prop.sharedMemPerBlockOptin - 8192 : 0;

@@ -29,6 +29,7 @@ typedef unsigned long long u64;
 #define T_BAD_ALIGNMENT 2u
 #define T_TOO_MANY 3u
 #define T_INTERNAL 4u
+#define T_POOL 5u  // internal: a list pool ran dry; the dispatcher rebuilds the target with a worst-case pool
 
 #define F_NO_NORMALIZE 1u
 #define F_NO_TRIM 2u

@@ -56,6 +56,7 @@ struct GV {           // one target's graph
     u32 pool_top, pool_end;  // 8-byte word indices from base
     u32 status;
     u32 nunits;       // record units in front of the pool: handles are < nunits; 0 switches the prefetches off
+    u32 pool_failed;  // the pool ran dry: the target is rebuilt with a worst-case pool (T_POOL), whatever else went wrong after
 };
 
 // The two sweeps (mergeNodes forwards, bestPath backwards) are chains of dependent loads: a vertex is first seen as
@@ -86,7 +87,7 @@ __device__ __forceinline__ u32 gv_in_cap(const GV& g, u32 h, u32 in_ptr) {
 }
 // a pool block of `words` 8-byte words behind one capacity word; returns the index of its first data word or 0
 __device__ __forceinline__ u32 gv_alloc(GV& g, u32 words, u32 cap) {
-    if (g.pool_top + words + 1 > g.pool_end) { g.status = T_INTERNAL; return 0; }
+    if (g.pool_top + words + 1 > g.pool_end) { g.status = T_POOL; g.pool_failed = 1; return 0; }
     const u32 off = g.pool_top;
     g.pool_top += words + 1;
     ((u64*)g.base)[off] = cap;
@@ -256,9 +257,10 @@ __device__ __forceinline__ void b2_append_out(const B2Ctx& c, u32 p, u32 dsth) {
         if (n >= 254u) { *c.s_status = T_TOO_MANY; return; }
         c.acc.dout[p] = (u8)(n + 1);
         ptr = n <= BB_OUT_CAP ? gv_inline_out(2 * p) : b2_hdr(c, 2 * p)->out_ptr;
-        if (n == BB_OUT_CAP) {  // the inline slots are full: the list moves into a pool block that can hold any degree
-            const u32 cap = c.A + 2, blk = atomicAdd(c.s_pool_top, cap + 1);
-            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_INTERNAL; return; }
+        const u32 have = n <= BB_OUT_CAP ? BB_OUT_CAP : (u32)((const u64*)c.base)[ptr - 1];
+        if (n == have) {  // full: the list moves into a pool block twice the size (a backbone vertex has at most A+1 out-edges)
+            const u32 cap = min(2u * have, max(c.A + 2, have + 1)), blk = atomicAdd(c.s_pool_top, cap + 1);
+            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.dout[p] = (u8)n; return; }
             ((u64*)c.base)[blk] = cap;
             const OSlot* o = (const OSlot*)(c.base + (size_t)ptr * 8);
             OSlot* no = (OSlot*)(c.base + (size_t)(blk + 1) * 8);
@@ -281,9 +283,10 @@ __device__ __forceinline__ void b2_append_in(const B2Ctx& c, u32 p, u32 srch) {
         if (n >= 254u) { *c.s_status = T_TOO_MANY; return; }
         c.acc.din[p] = (u8)(n + 1);
         ptr = n <= REC_IN_CAP ? gv_inline_in(2 * p) : b2_hdr(c, 2 * p)->in_ptr;
-        if (n == REC_IN_CAP) {
-            const u32 cap = c.A + 2, words = (cap + 1) / 2, blk = atomicAdd(c.s_pool_top, words + 1);
-            if (blk + words + 1 > c.pool_end) { *c.s_status = T_INTERNAL; return; }
+        const u32 have = n <= REC_IN_CAP ? REC_IN_CAP : (u32)((const u64*)c.base)[ptr - 1];
+        if (n == have) {
+            const u32 cap = min(2u * have, max(c.A + 2, have + 1)), words = (cap + 1) / 2, blk = atomicAdd(c.s_pool_top, words + 1);
+            if (blk + words + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.din[p] = (u8)n; return; }
             ((u64*)c.base)[blk] = cap;
             const u32* in = (const u32*)(c.base + (size_t)ptr * 8);
             u32* ni = (u32*)(c.base + (size_t)(blk + 1) * 8);
@@ -367,7 +370,7 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
         s_ins = nbb; s_status = T_OK;
         s_enter_out = 1; s_exit_in = 1;
         s_pool_top = c.exit_in + (c.A + 2 + 1) / 2;
-        if (s_pool_top > c.pool_end) s_status = T_INTERNAL;
+        if (s_pool_top > c.pool_end) s_status = T_POOL;
         else {
             ((u64*)c.base)[c.enter_out - 1] = c.A + 2;
             ((u64*)c.base)[c.exit_in - 1] = c.A + 2;
@@ -689,6 +692,7 @@ __device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx&
     c.g.pool_top = a.tgt_pool_top[t];
     c.g.pool_end = pool_begin + a.pool_cap[t];
     c.g.status = T_OK;
+    c.g.pool_failed = 0;
     c.g.nunits = (a.flags & F_NO_PREFETCH) ? 0u : pool_begin / 16u;
     c.S = a.gscratch + a.gscratch_off[t];
     c.scap = a.gscratch_cap[t];
@@ -909,6 +913,7 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
     if (lane == 0) {
         a.tgt_pool_top[t] = g.pool_top;
         if (status == T_OK) status = g.status;
+        if (g.pool_failed) status = T_POOL;
         if (status != T_OK) a.tgt_status[t] = status;
     }
     __syncwarp();

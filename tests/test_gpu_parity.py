@@ -301,3 +301,30 @@ def test_staged_upload_matches_resident_run(api, synth, monkeypatch):
             r = eng.collect()
             assert [r.frags(t) for t in range(r.n_targets)] == want
         eng.close()
+
+
+def test_pool_exhaustion_rebuilds_with_worst_case_pool(api, synth, monkeypatch):
+    """A target whose list pool runs dry (high coverage: backbone in-lists beyond the 12 inline slots, merge survivors
+    beyond 6) is rebuilt with a worst-case pool; DGC_TEST_TINY_POOL makes every first-pass pool too small."""
+    o = Oracle()
+    sb = synth.gen_batch(seed=41, L=1200, cov=80, t0=0, nt=12)
+    pb = api.PackedBatch.from_synth(sb)
+    want = [o.consensus(1200, sb.target_alns(t), mode=MODE_PIPELINE, trim=20, min_weight=8, min_len=100)["frags"] for t in range(12)]
+    eng = api.Consensus(min_cov=8, min_len=100, trim=20)
+    res = eng(pb)
+    eng.close()
+    assert list(res.status) == [api.T_OK] * 12 and [res.frags(t) for t in range(12)] == want
+    monkeypatch.setenv("DGC_TEST_TINY_POOL", "1")
+    monkeypatch.setenv("DGC_STAGE_MIN_BYTES", "1")
+    monkeypatch.setenv("DGC_STAGE_PIECE_BYTES", str(1 << 20))
+    eng = api.Consensus(min_cov=8, min_len=100, trim=20)
+    res = eng.run(eng.upload(pb))                  # simple path
+    assert list(res.status) == [api.T_OK] * 12 and [res.frags(t) for t in range(12)] == want
+    assert eng.timings()["chunks"] >= 2            # the rebuild ran as a chunk of its own
+    eng.submit(pb)                                 # staged path
+    res = eng.collect()
+    assert list(res.status) == [api.T_OK] * 12 and [res.frags(t) for t in range(12)] == want
+    eng.close()
+    monkeypatch.setenv("DGC_TEST_TINY_POOL", "0")
+    eng = api.Consensus(min_cov=8, min_len=100, trim=20)   # the flag is process-wide: switch it off again
+    eng.close()
