@@ -135,8 +135,8 @@ struct ProgramOpts {
     std::string input = "-";
     // dispatcher
     int gpus = 0;           // 0 = all visible devices
-    size_t batchTargets = 2048;
-    size_t batchBytes = 1ull << 30;
+    size_t batchTargets = 1024;
+    size_t batchBytes = 512ull << 20;
     bool stats = false;
 };
 

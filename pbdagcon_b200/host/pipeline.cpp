@@ -59,6 +59,14 @@ public:
         cv_space_.notify_one();
         return true;
     }
+    bool try_pop(T& v) {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (q_.empty()) return false;
+        v = std::move(q_.front());
+        q_.pop_front();
+        cv_space_.notify_one();
+        return true;
+    }
     void close() {
         std::lock_guard<std::mutex> lk(mu_);
         closed_ = true;
@@ -240,11 +248,26 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
         if (!rc) { rc = code; err = msg; }
     }
 
-    void start(size_t pool) {
-        for (size_t i = 0; i < pool; i++) {
-            const size_t acap = std::min<size_t>(o.batchBytes + (o.batchBytes >> 3), 8ull << 30);
-            free_batches.push(std::unique_ptr<HostBatch>(new HostBatch(pinned, acap, 64 * o.batchTargets, o.batchTargets + 1)));
+    // Host batches are page-locked, which costs about a second per few GB: they are made when a packer first needs
+    // one (at most `pool` of them), not up front, so a small input never pays for the whole ring.
+    size_t pool_max = 0, pool_made = 0;
+    std::mutex pool_mu;
+    bool take_batch(std::unique_ptr<HostBatch>& hb) {
+        if (free_batches.try_pop(hb)) return true;
+        {
+            std::lock_guard<std::mutex> lk(pool_mu);
+            if (pool_made < pool_max) {
+                pool_made++;
+                const size_t acap = std::min<size_t>(o.batchBytes + (o.batchBytes >> 3), 8ull << 30);
+                hb.reset(new HostBatch(pinned, acap, 64 * o.batchTargets, o.batchTargets + 1));
+                return true;
+            }
         }
+        return free_batches.pop(hb);
+    }
+
+    void start(size_t pool) {
+        pool_max = pool;
         const int np = std::max(1, o.threads);
         live_packers = np;
         threads.emplace_back([this] {
@@ -262,7 +285,9 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                 std::unique_ptr<WorkUnit> u;
                 while (units.pop(u)) {
                     std::unique_ptr<HostBatch> hb;
-                    if (!free_batches.pop(hb)) break;
+                    try {
+                        if (!take_batch(hb)) break;
+                    } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); break; }
                     try {
                         hb->clear();
                         hb->seq = u->seq;
@@ -327,17 +352,17 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         return DGC_E_NODEVICE;
     }
     const int G = opts.gpus > 0 ? std::min(opts.gpus, ndev) : ndev;
+    // the reader and the packers start at once: scanning the text overlaps the CUDA context and handle creation
+    Front fr(opts, true, stats);
+    fr.start((size_t)G * DGC_MAX_INFLIGHT + 2);
     std::vector<dgc_handle*> hs((size_t)G, nullptr);
     auto destroy_all = [&] { for (auto h : hs) if (h) dgc_destroy(h); };
     for (int g = 0; g < G; g++) {
         dgc_opts o{};
         o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = g;
         const int rc = dgc_create(&o, &hs[(size_t)g]);
-        if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); destroy_all(); return rc; }
+        if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); fr.stop(); destroy_all(); return rc; }
     }
-
-    Front fr(opts, true, stats);
-    fr.start((size_t)G * DGC_MAX_INFLIGHT + 2);
 
     std::deque<std::unique_ptr<HostBatch>> inflight;  // in submit (= input) order; batch k runs on GPU k % G
     std::vector<int> on_gpu((size_t)G, 0);
