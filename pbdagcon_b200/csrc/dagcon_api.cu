@@ -110,7 +110,8 @@ struct Slot {
     DevBuf o_off, o_len, o_start, o_flags, o_nI, o_nE, o_tkept, norm;
     // per-target arrays
     DevBuf t_status, t_V, t_E, t_cols, t_ne, t_nv, t_cons_len, t_nfrag, t_cons_coff, t_frag_coff, totals;
-    DevBuf rec_off, pos_off, pool_cap, t_pool_top, cons_off, frag_off, frag_cap, gs_off, gs_cap;
+    DevBuf rec_off, pos_off, pool_cap, t_pool_top, cons_off, frag_off, frag_cap, gs_off, gs_cap, order;
+    HostBuf hp_order;     // sweep order per chunk: longest graphs first
     HostBuf hp_plan_in;   // status, V, E, cols read back after the plan kernel
     HostBuf hp_plan_out;  // the offset arrays
     // chunk arenas
@@ -356,6 +357,18 @@ int launch_serial(Slot& s, dgc_dbatch& db, const Chunk& c, int stop_after) {
     sa.gscratch = s.gscratch.as<u32>(); sa.gscratch_off = s.gs_off.as<u64>(); sa.gscratch_cap = s.gs_cap.as<u32>();
     sa.cons = s.cons.as<u8>(); sa.cons_off = s.cons_off.as<u64>(); sa.frags = s.frags.as<int>(); sa.frag_off = s.frag_off.as<u64>();
     sa.frag_cap = s.frag_cap.as<u32>(); sa.tgt_cons_len = s.t_cons_len.as<u32>(); sa.tgt_nfrag = s.t_nfrag.as<u32>();
+    // Longest graphs first: a launch of more targets than resident warps runs in waves, and a long chain that starts
+    // late is the tail of the whole launch.  The four warps of a block also get graphs of similar size this way.
+    {
+        const size_t T = db.T;
+        CU(s.hp_order.ensure(4 * (T + 1))); CU(s.order.ensure(4 * (T + 1)));
+        const uint32_t* hp_V = s.hp_plan_in.as<uint32_t>() + (T + 1);
+        uint32_t* ord = s.hp_order.as<uint32_t>() + c.first;
+        for (uint32_t i = 0; i < c.count; i++) ord[i] = c.first + i;
+        std::stable_sort(ord, ord + c.count, [&](uint32_t x, uint32_t y) { return hp_V[x] > hp_V[y]; });
+        CU(cudaMemcpyAsync(s.order.as<u32>() + c.first, ord, 4ull * c.count, cudaMemcpyHostToDevice, st));
+        sa.order = s.order.as<u32>();
+    }
     const uint32_t warps_per_block = WARP_KERNEL_THREADS / 32;   // one warp per target
     const uint32_t grid = (c.count + warps_per_block - 1) / warps_per_block;
     if (stop_after >= 2 && !(o.flags & (DGC_F_NO_MERGE | DGC_F_SPLIT_SWEEPS))) {

@@ -505,6 +505,7 @@ struct Serial2Args {
     u32* tgt_pool_top;
     const u32* tgt_nv;
     u8* rec;
+    const u32* order;       // order[first + i] = target of the launch's i-th warp (longest graphs first), or nullptr
     u32* gscratch;          // the group snapshot stack of mergeInNodes
     const u64* gscratch_off;
     const u32* gscratch_cap;
@@ -684,7 +685,7 @@ __device__ __forceinline__ void m2_queue_append(const GV& g, u32 ready, bool min
 __device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx& c) {
     const u32 idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (idx >= a.count) return false;
-    t = a.first + idx;
+    t = a.order ? a.order[a.first + idx] : a.first + idx;
     if (a.tgt_status[t] != T_OK) return false;
     c.g.base = a.rec + (size_t)REC_UNIT * a.rec_off[t];
     c.g.nbb = a.tgt_tlen[t] + 2;
