@@ -161,7 +161,7 @@ class PackedBatch:
 
 
 class Results:
-    """Copy of a dgc_results (the handle's memory is only valid until the next collect)."""
+    """Copy of a dgc_results (the handle's memory is only valid until the next submit, collect or run)."""
 
     def __init__(self, r: CResults):
         T, F = r.n_targets, r.n_frags
