@@ -20,7 +20,8 @@
 #define NW_TR 1024u  // raw columns normalised per tile: 32 per lane
 #define NW_MG 256u   // look-ahead margin staged behind the tile: 8 per lane
 #define NW_W (NW_TR + NW_MG)
-#define NW_WARPS 8
+#define NW_WARPS 4
+#define NW_STG 66u   // u16 per lane in the output staging area: 64 columns + padding against bank conflicts
 #define AF_RETRY 2u  // needs the serial kernel (look-ahead left the staged window)
 
 struct NwSmem {
@@ -28,6 +29,7 @@ struct NwSmem {
     uint4 t[NW_W / 16];
     u8 ts[NW_W];  // target bases of the staged window, in order
     u8 qs[NW_W];  // query bases
+    u16 stage[32 * NW_STG];  // every lane's output columns of the tile (a raw column yields at most two)
 };
 
 __device__ __forceinline__ u32 nw_byte(const u32* w, int j) { return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu; }
@@ -116,7 +118,7 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, u32 lane) {
     return v;
 }
 
-__global__ void __launch_bounds__(NW_WARPS * 32, 2) k_normalize_warp(NormArgs a) {
+__global__ void __launch_bounds__(NW_WARPS * 32, 5) k_normalize_warp(NormArgs a) {
     __shared__ NwSmem sm_all[NW_WARPS];
     const u32 lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const u32 ai = a.aln_first + blockIdx.x * NW_WARPS + wid;
@@ -196,7 +198,10 @@ __global__ void __launch_bounds__(NW_WARPS * 32, 2) k_normalize_warp(NormArgs a)
         // ---- speculative pass + repair rounds (counts only)
         const bool has_last = nvalid && (c0 + col0 + nvalid == n);
         u32 lead_in = lane == 0 ? carry : 0u, lead_out = lead_in;
-        u32 nout = nw_chunk<false>(qw, tw, nvalid, has_last, ot0, oq0, lead_out, sm.ts, sm.qs, availT, availQ, more, overflow, nullptr);
+        // every pass writes the lane's columns to its staging row: when the speculation holds (the common case) the
+        // transducer has run once, not twice, and the tile goes out with coalesced stores
+        u16* const stg = sm.stage + lane * NW_STG;
+        u32 nout = nw_chunk<true>(qw, tw, nvalid, has_last, ot0, oq0, lead_out, sm.ts, sm.qs, availT, availQ, more, overflow, stg);
         for (;;) {
             u32 prev = __shfl_up_sync(0xFFFFFFFFu, lead_out, 1);
             if (lane == 0) prev = lead_in;
@@ -204,14 +209,18 @@ __global__ void __launch_bounds__(NW_WARPS * 32, 2) k_normalize_warp(NormArgs a)
             if (!__any_sync(0xFFFFFFFFu, bad)) break;
             if (bad) {
                 lead_in = prev; lead_out = prev;
-                nout = nw_chunk<false>(qw, tw, nvalid, has_last, ot0, oq0, lead_out, sm.ts, sm.qs, availT, availQ, more, overflow, nullptr);
+                nout = nw_chunk<true>(qw, tw, nvalid, has_last, ot0, oq0, lead_out, sm.ts, sm.qs, availT, availQ, more, overflow, stg);
             }
         }
         if (__any_sync(0xFFFFFFFFu, overflow != 0)) { overflow = 1; break; }
         // ---- emit
         const u32 oinc = warp_incl_scan(nout, lane);
-        u32 l2 = lead_in;
-        nw_chunk<true>(qw, tw, nvalid, has_last, ot0, oq0, l2, sm.ts, sm.qs, availT, availQ, more, overflow, out + m + (oinc - nout));
+        __syncwarp();
+#pragma unroll 1
+        for (u32 l = 0; l < 32; l++) {  // row l of the staging area, by the whole warp
+            const u32 nl = __shfl_sync(0xFFFFFFFFu, nout, l), dl = __shfl_sync(0xFFFFFFFFu, oinc - nout, l);
+            for (u32 i = lane; i < nl; i += 32) out[m + dl + i] = sm.stage[l * NW_STG + i];
+        }
         m += __shfl_sync(0xFFFFFFFFu, oinc, 31);
         carry = __shfl_sync(0xFFFFFFFFu, lead_out, 31);
     }

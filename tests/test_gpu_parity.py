@@ -328,3 +328,41 @@ def test_pool_exhaustion_rebuilds_with_worst_case_pool(api, synth, monkeypatch):
     monkeypatch.setenv("DGC_TEST_TINY_POOL", "0")
     eng = api.Consensus(min_cov=8, min_len=100, trim=20)   # the flag is process-wide: switch it off again
     eng.close()
+
+
+def test_config2_shape_invariants_at_scale(api, synth):
+    """BASELINE configs[1] shape (8 kb x 30x, -c 8 -m 500 -t 50) at 1500 targets: the resident run, the staged submit and
+    a run squeezed into many chunks agree bit for bit, a second run reproduces the first, every target yields
+    consensus, and a sample matches the oracle."""
+    import hashlib
+    nt, L = 1500, 8000
+    pieces = [synth.gen_batch(seed=2, L=L, cov=30, t0=t0, nt=125) for t0 in range(0, nt, 125)]
+    pb = api.PackedBatch.from_synth(synth.concat(pieces))
+
+    def digest(res):
+        h = hashlib.md5()
+        for t in range(res.n_targets):
+            h.update(bytes([int(res.status[t])]))
+            for a, b, s in res.frags(t):
+                h.update(b"%d_%d:" % (a, b) + s)
+        return h.hexdigest()
+
+    eng = api.Consensus(min_cov=8, min_len=500, trim=50)
+    db = eng.upload(pb)
+    r1 = eng.run(db)
+    d1 = digest(r1)
+    assert digest(eng.run(db)) == d1, "a second run over the same resident batch differs"
+    eng.free(db)
+    eng.submit(pb)
+    assert digest(eng.collect()) == d1, "staged submit differs from the resident run"
+    eng.close()
+    eng = api.Consensus(min_cov=8, min_len=500, trim=50, scratch_bytes=2 << 30)
+    r3 = eng(pb)
+    assert eng.timings()["chunks"] >= 4 and digest(r3) == d1, "chunked run differs"
+    eng.close()
+    assert all(int(s) == api.T_OK for s in r1.status)
+    assert all(sum(len(f[2]) for f in r1.frags(t)) > 0.5 * L for t in range(nt))
+    o = Oracle()
+    for t in range(0, nt, 97):
+        alns = pieces[t // 125].target_alns(t % 125)
+        assert r1.frags(t) == o.consensus(L, alns, mode=MODE_PIPELINE, trim=50, min_weight=8, min_len=500)["frags"], f"target {t}"
