@@ -704,9 +704,10 @@ __device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx&
 #define WARP_KERNEL_THREADS 128
 #endif
 #ifndef MERGE_MIN_BLOCKS
-#define MERGE_MIN_BLOCKS 10  // resident 128-thread blocks per SM k_merge_nodes2's register allocation must allow: 48 registers,
-                             // 40 warps per SM.  Measured on B200 (10 000 targets): 8 blocks 168 ms, 9-10 blocks 133-135 ms, 12 blocks
-                             // (40 registers, spills) 143 ms, 16 blocks 161 ms
+#define MERGE_MIN_BLOCKS 9   // resident 128-thread blocks per SM the sweeps' register allocation must allow: 56 registers,
+                             // 36 warps per SM.  Measured on B200, 10 000 targets, mergeNodes alone: 8 blocks 168 ms, 9-10 blocks
+                             // 133-135 ms, 12 blocks (40 registers, spills) 143 ms, 16 blocks 161 ms; both sweeps fused: 9 blocks
+                             // 189 ms, 10 blocks 193 ms, 11 blocks 204 ms
 #endif
 
 // mergeNodes :129-160
