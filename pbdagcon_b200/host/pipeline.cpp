@@ -283,11 +283,16 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
         for (int i = 0; i < np; i++) {
             threads.emplace_back([this] {
                 std::unique_ptr<WorkUnit> u;
-                while (units.pop(u)) {
+                for (;;) {
+                    // A packer takes its host batch BEFORE it takes a unit: units are handed out in input order, so the
+                    // oldest unit not yet packed is always in the hands of a packer that can finish it.  (Unit first,
+                    // batch second, lets younger units take the last free batches while the consumer waits for the
+                    // oldest one and therefore never collects and recycles: a deadlock, seen with many tiny batches.)
                     std::unique_ptr<HostBatch> hb;
                     try {
                         if (!take_batch(hb)) break;
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); break; }
+                    if (!units.pop(u)) { free_batches.push(std::move(hb)); break; }  // hand the batch on: another packer may be waiting for one just to find the input exhausted
                     try {
                         hb->clear();
                         hb->seq = u->seq;
