@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
     const u32 ENTER = 0, EXIT = L + 1, nbb = L + 2;
     const u32 a0 = a.tgt_aln_begin[t], a1 = a.tgt_aln_begin[t + 1];
     __shared__ u32 sa[BT / 32], sb[BT / 32], s_cur[TILE];
-    __shared__ u32 s_carry_t, s_carry_i, s_last, s_ins, s_pool_top, s_status, s_enter_out, s_exit_in;
+    __shared__ u32 s_pool_top, s_status, s_enter_out, s_exit_in;
     extern __shared__ __align__(16) u8 s_dyn[];
     u8* accbase = (nbb <= a.smem_positions) ? s_dyn : a.gacc + 9ull * a.acc_off[t];
     B2Ctx c;
@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
         }
     }
     if (tid == 0) {
-        s_ins = nbb; s_status = T_OK;
+        s_status = T_OK;
         s_enter_out = 1; s_exit_in = 1;
         s_pool_top = c.exit_in + (c.A + 2 + 1) / 2;
         if (s_pool_top > c.pool_end) s_status = T_POOL;
@@ -382,12 +382,13 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
     __syncthreads();
     if (s_status != T_OK) { if (tid == 0) a.tgt_status_out[t] = s_status; return; }
 
+    u32 ins_base = nbb;  // id of the next insertion vertex
     for (u32 k = a0; k < a1; k++) {
         if (a.a_flags[k] & AF_SKIP) continue;
         const u32 n = a.a_len[k], start = a.a_start[k];
         const u16* cols = a.norm + a.a_off[k];
-        if (tid == 0) { s_carry_t = 0; s_carry_i = 0; s_last = ENTER; }
-        __syncthreads();
+        // block-uniform replay state, kept in registers by every thread: no serial section, no barrier to publish it
+        u32 carry_t = 0, carry_i = 0, last = ENTER;
         for (u32 c0 = 0; c0 < n; c0 += TILE) {
             const u32 cb = c0 + tid * CPT;
             u32 q[CPT], tc[CPT], kind[CPT];  // kind: 0 none, 1 match, 2 deletion, 3 insertion
@@ -411,7 +412,7 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
             block_scan2(nadv | (nins << 16), lastp, ex_s, ex_m, tot_s, tot_m, sa, sb);
             u32 bbpos[CPT], cur[CPT];
             {
-                u32 tb = start + s_carry_t + (ex_s & 0xFFFFu), ib = s_ins + s_carry_i + (ex_s >> 16);
+                u32 tb = start + carry_t + (ex_s & 0xFFFFu), ib = ins_base + carry_i + (ex_s >> 16);
 #pragma unroll
                 for (int j = 0; j < CPT; j++) {
                     bbpos[j] = tb;
@@ -422,7 +423,8 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
                 }
             }
             __syncthreads();
-            u32 prev = ex_m ? s_cur[ex_m - 1] : s_last;
+            u32 prev = ex_m ? s_cur[ex_m - 1] : last;
+            const u32 tile_last = tot_m ? s_cur[tot_m - 1] : last;  // read before the next tile's scan lets s_cur be rewritten
 #pragma unroll
             for (int j = 0; j < CPT; j++) {
                 const u32 p = bbpos[j];
@@ -442,20 +444,18 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
                     prev = cur[j];
                 }
             }
-            __syncthreads();
-            if (tid == 0) {
-                s_carry_t += tot_s & 0xFFFFu;
-                s_carry_i += tot_s >> 16;
-                if (tot_m) s_last = s_cur[tot_m - 1];
-            }
-            __syncthreads();
+            // The next tile (or alignment) passes the scan's barriers before it touches s_cur or any list again, so
+            // this tile's list writes and s_cur reads are ordered against it without a barrier of their own.
+            carry_t += tot_s & 0xFFFFu;
+            carry_i += tot_s >> 16;
+            last = tile_last;
         }
-        if (tid == 0) {  // addEdge(prevVtx, _exitVtx) :106
-            b2_edge(c, s_last, EXIT);
-            s_ins += s_carry_i;
-        }
-        __syncthreads();
+        if (n == 0) __syncthreads();           // an empty alignment ran no scan: order its exit edge by hand
+        if (tid == 0) b2_edge(c, last, EXIT);  // addEdge(prevVtx, _exitVtx) :106
+        ins_base += carry_i;
+        if (n == 0) __syncthreads();
     }
+    __syncthreads();
     // fold the running sums into the backbone headers, then give every insertion vertex the coverage of the
     // backbone vertex it maps to (bestPath reads _g[_bbMap[v]].coverage, :407)
     const u8* bbstr = a.tgt_bb_off ? a.arena + a.tgt_bb_off[t] : nullptr;
@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
         *hp = h;
         if (p <= L) ((OSlot*)(c.base + (size_t)h.out_ptr * 8))[0].cv = c.acc.c[p];
     }
-    const u32 nv = s_ins;
+    const u32 nv = ins_base;
     for (u32 v = nbb + tid; v < nv; v += BT) {
         Hdr* hv = b2_hdr(c, v + nbb);
         const u32 bm = (u32)hv->cov;
