@@ -195,10 +195,10 @@ __device__ __noinline__ void gv_reap(GV& g, u32 ni) {
 }
 
 // ------------------------------------------------------------------------------------------
-// K2: graph construction (ctor :16-62, addAln :64-107, addEdge :109-127), one 256-thread block per target.
+// K2: graph construction (ctor :16-62, addAln :64-107, addEdge :109-127), one 512-thread block per target.
 // Alignments are replayed in input order (every adjacency list is ordered by the alignment that first created
 // each edge); inside one alignment every vertex is entered and left at most once, so its columns are processed in
-// parallel, 1024 per tile: block scans give each column its backbone position, its insertion-vertex id and its
+// parallel, 1024 per tile (512 threads x 2): block scans give each column its backbone position, its insertion-vertex id and its
 // predecessor on the path.  Per backbone position the running sums (coverage, match weight, count of the ctor
 // edge p->p+1, last target base, list lengths) stay in shared memory for the whole replay and are folded into
 // the records once at the end; insertion records are written exactly once.
@@ -322,7 +322,10 @@ __device__ __forceinline__ void b2_edge(const B2Ctx& c, u32 prev, u32 cur) {
     else *(u32*)(c.base + (size_t)ch * REC_UNIT + REC_IN_OFF) = ph;
 }
 
-__global__ void __launch_bounds__(BT) k_build_graph2(Build2Args a) {
+#ifndef BUILD_MIN_BLOCKS
+#define BUILD_MIN_BLOCKS 3  // 40 registers: three 512-thread blocks per SM also when no shared memory limits them (gacc)
+#endif
+__global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Args a) {
     const u32 t = a.first + blockIdx.x;
     if (a.tgt_status[t] != T_OK) return;
     const u32 tid = threadIdx.x;
