@@ -25,11 +25,15 @@
 #define AF_RETRY 2u  // needs the serial kernel (look-ahead left the staged window)
 
 struct NwSmem {
-    uint4 q[NW_W / 16];
-    uint4 t[NW_W / 16];
+    union {  // the staged raw strings are in registers by the time the transducer writes its output rows
+        struct {
+            uint4 q[NW_W / 16];
+            uint4 t[NW_W / 16];
+        };
+        u16 stage[32 * NW_STG];  // every lane's output columns of the tile (a raw column yields at most two)
+    };
     u8 ts[NW_W];  // target bases of the staged window, in order
     u8 qs[NW_W];  // query bases
-    u16 stage[32 * NW_STG];  // every lane's output columns of the tile (a raw column yields at most two)
 };
 
 __device__ __forceinline__ u32 nw_byte(const u32* w, int j) { return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu; }
@@ -118,7 +122,7 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, u32 lane) {
     return v;
 }
 
-__global__ void __launch_bounds__(NW_WARPS * 32, 5) k_normalize_warp(NormArgs a) {
+__global__ void __launch_bounds__(NW_WARPS * 32, 7) k_normalize_warp(NormArgs a) {
     __shared__ NwSmem sm_all[NW_WARPS];
     const u32 lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const u32 ai = a.aln_first + blockIdx.x * NW_WARPS + wid;
