@@ -366,7 +366,7 @@ def main():
     ap.add_argument("--sub", type=int, default=0, help="targets per dgc_submit in the e2e arm (0 = the whole step in one "
                     "submit: the library stages the upload itself)")
     ap.add_argument("--tpw", type=int, default=0, help="targets per warp in the serial kernels (0 = auto)")
-    ap.add_argument("--scratch-gb", type=int, default=72)
+    ap.add_argument("--scratch-gb", type=int, default=112)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-trace", action="store_true", help="print the device timings of every collected sub-batch")
     ap.add_argument("--flags", type=int, default=0, help="extra dgc_opts.flags (tuning, e.g. 256 = no prefetch)")

@@ -481,7 +481,7 @@ int retry_pool_failures(Slot& s, dgc_dbatch& db, int stop_after) {
     uint32_t* p_pcap = p_gcap + (T + 1);
     CU(cudaMemcpyAsync(hp_status, s.t_status.p, 4 * T, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    const uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
+    const uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (112ull << 30);
     size_t t = 0;
     while (t < T) {
         if (hp_status[t] != T_POOL) { t++; continue; }
@@ -577,7 +577,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     uint32_t* p_fcap = (uint32_t*)(p_gs + (T + 1));
     uint32_t* p_gcap = p_fcap + (T + 1);
     uint32_t* p_pcap = p_gcap + (T + 1);
-    uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
+    uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (112ull << 30);
     std::vector<Chunk> chunks;
     Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
     uint64_t out_cons_cap = 0, out_frag_cap = 0;
@@ -766,7 +766,7 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
     uint32_t* p_fcap = (uint32_t*)(p_gs + (T + 1));
     uint32_t* p_gcap = p_fcap + (T + 1);
     uint32_t* p_pcap = p_gcap + (T + 1);
-    const uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (72ull << 30);
+    const uint64_t budget = o.scratch_bytes ? o.scratch_bytes : (112ull << 30);
 
     Chunk cur{0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t built_to = 0, planned_to = 0, pend_maxL2 = 0, nchunks = 0;
