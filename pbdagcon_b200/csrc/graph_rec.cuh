@@ -848,17 +848,25 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
                             u32* inx = nullptr;
                             u32 xin = 0;
                             if (leader) { hx = gv_hdr(g, x); xin = hx->deg & 0xFFFFu; inx = gv_in(g, hx->in_ptr); }
+                            // the leader collects the (at most five) members that leave this list, then compacts the
+                            // list in ONE pass whose loads do not depend on each other
+                            u32 r0 = NIL, r1 = NIL, r2 = NIL, r3 = NIL, r4 = NIL, nr = 0;
                             for (u32 mm = M & ~(1u << la); mm; mm &= mm - 1) {
                                 const u32 j = (u32)__ffs((int)mm) - 1;
                                 const u32 nj = __shfl_sync(M, sl.dst, j);
-                                if (leader && ((Mx >> j) & 1u)) {
-                                    u32 i = 0;
-                                    while (i < xin && inx[i] != nj) i++;
-                                    if (i == xin) status = T_INTERNAL;
-                                    else { for (; i + 1 < xin; i++) inx[i] = inx[i + 1]; xin--; }
-                                }
+                                if (leader && ((Mx >> j) & 1u)) { r4 = r3; r3 = r2; r2 = r1; r1 = r0; r0 = nj; nr++; }
                             }
                             if (leader) {
+                                u32 w = 0;
+#pragma unroll 4
+                                for (u32 i = 0; i < xin; i++) {
+                                    const u32 e = inx[i];
+                                    if (e == r0 || e == r1 || e == r2 || e == r3 || e == r4) continue;
+                                    if (w != i) inx[w] = e;
+                                    w++;
+                                }
+                                if (w + nr != xin) status = T_INTERNAL;
+                                xin = w;
                                 if (!is_a) inx[xin++] = an;
                                 hx->deg = (hx->deg & 0xFFFF0000u) | xin;
                             }
