@@ -48,7 +48,7 @@ def gen_workload(seed, L, cov, t0, nt, sub, threads):
     jobs = [(t0 + s, min(piece, nt - s)) for s in range(0, nt, piece)]
     with ThreadPoolExecutor(max_workers=max(1, threads)) as ex:
         pieces = list(ex.map(lambda j: synth.gen_batch(seed, L, cov, j[0], j[1]), jobs))
-    per = max(1, sub // piece)
+    per = max(1, -(-sub // piece))
     return [synth.concat(pieces[i:i + per]) for i in range(0, len(pieces), per)]
 
 
@@ -271,7 +271,7 @@ def run_gpu(args):
             got += 1
             if args.e2e_trace:
                 tmx = eng.timings()
-                print("e2e sub-batch", got, {k: round(v, 1) for k, v in tmx.items() if k.startswith("ms_")},
+                print("e2e sub-batch", got, "chunks", tmx["chunks"], "launches", tmx["launches"], {k: round(v, 1) for k, v in tmx.items() if k.startswith("ms_")},
                       "t=%.1f ms" % ((time.perf_counter() - e2e_t0[0]) * 1e3), file=sys.stderr)
             nb += int(np.ctypeslib.as_array(r.frag_seq_len, (r.n_frags,)).astype(np.int64).sum()) if r.n_frags else 0
             d2h += int(r.seq_bytes) + 8 * r.n_frags + 16 * r.n_targets
