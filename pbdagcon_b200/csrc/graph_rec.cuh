@@ -747,6 +747,30 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
         }
         // ---- mergeOutNodes(u), then mark the out-edges visited and enqueue the successors that became ready
         u32 nout = hu.deg >> 16;
+        if (nout == 1) {
+            // One successor: nothing for mergeOutNodes to group (:231 needs two).  Most vertices are such chain links
+            // (an insertion run, a backbone stretch every read agrees on); they take this warp-uniform short cut
+            // instead of the list machinery below: visit the edge, enqueue the successor if it became ready.
+            OSlot* o = gv_out(g, hu.out_ptr);
+            const OSlot s0 = *o;
+            Hdr* hv = gv_hdr(g, s0.dst);
+            const uint2 d0 = *(const uint2*)hv;
+            const bool fresh = !(s0.cv & VISBIT);
+            u32 bfv = d0.x + (fresh ? 0x10000u : 0u);
+            const bool ready = (bfv >> 16) == (d0.y & 0xFFFFu);  // notVisited == 0 (:150-157)
+            if (ready && (bfv & (NF_QUEUED << 8))) status = T_INTERNAL;
+            if (ready) bfv |= NF_QUEUED << 8;
+            __syncwarp();
+            if (lane == 0) {
+                if (fresh) o->cv = s0.cv | VISBIT;
+                if (bfv != d0.x) hv->bfv = bfv;
+                if (ready) gv_hdr(g, tail)->best = s0.dst;
+            }
+            if (ready) tail = s0.dst;
+            __syncwarp();
+            head = pu->best;
+            continue;
+        }
         if (nout > 32) {  // enter (one edge per alignment start): scalar
             if (lane == 0) {
                 m2_merge_out_generic(c, u);
