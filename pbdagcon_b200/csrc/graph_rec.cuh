@@ -988,6 +988,14 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
         // ---- the best out-edge: first maximum of the per-edge scores in list order
         float best_score = -FLT_MAX;
         u32 best_dst = NIL;
+        if (nout == 1) {  // a chain link: its one edge is the best edge; every lane computes it, no reduction
+            const OSlot s = *gv_out(g, hn.out_ptr);
+            const Hdr hd = *gv_hdr(g, s.dst);
+            best_dst = s.dst;
+            if ((hd.bfv & (NF_BACKBONE << 8)) && hd.weight == 1) best_score = __fsub_rn(hd.score, 10.0f);
+            else best_score = __fadd_rn(__fsub_rn((float)(int)(s.cv & ~VISBIT), __fmul_rn((float)hd.cov, 0.5f)), hd.score);
+            if (!(best_score > -FLT_MAX)) best_dst = NIL;  // the reference's strict `>` against its initial value
+        } else
         for (u32 b0 = 0; b0 < nout; b0 += 32) {
             const bool have = b0 + lane < nout;
             float ns = -FLT_MAX;
