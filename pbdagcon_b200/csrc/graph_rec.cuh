@@ -1016,6 +1016,19 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
             if (cs > best_score) { best_score = cs; best_dst = cd; }  // strict >: an earlier chunk's maximum stays
         }
         // ---- count this vertex off at its predecessors; those with all successors scored join the queue
+        if (nin == 1) {  // a chain link again: one predecessor, handled warp-uniformly without the append machinery
+            const u32 s = gv_in(g, hn.in_ptr)[0];
+            Hdr* hs = gv_hdr(g, s);
+            const u32 sdeg = hs->deg;
+            const u32 k = (u32)(hs->cnt + 1);
+            const bool ready = k == (sdeg >> 16);
+            __syncwarp();
+            if (lane == 0) {
+                hs->cnt = (int)k;
+                if (ready) { hs->best = NIL; gv_hdr(g, tail)->best = s; }
+            }
+            if (ready) tail = s;
+        } else
         for (u32 b0 = 0; b0 < nin; b0 += 32) {
             const bool have = b0 + lane < nin;
             u32 s = NIL;
