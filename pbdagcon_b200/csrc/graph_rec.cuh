@@ -804,10 +804,12 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
             sl = gv_out(g, hu.out_ptr)[lane];
             const u8* rv = g.base + (size_t)sl.dst * REC_UNIT;
             d = *(const uint2*)rv;
+#ifndef GV_NO_PREFETCH
             const uint4 o01 = *(const uint4*)(rv + REC_OUT_OFF);  // the successor's first two out-slots (inline position)
             if (g.nunits) pf_l2(rv + 32);
             if (d.y >> 16) gv_prefetch_rec(g, o01.x);
             if ((d.y >> 16) > 1) gv_prefetch_rec(g, o01.z);
+#endif
         }
         {
             const bool cand = have && (d.y & 0xFFFFu) == 1;
@@ -1038,13 +1040,17 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
                 Hdr* hs = gv_hdr(g, s);
                 const u32 sdeg = hs->deg;
                 const u32 k = (u32)(hs->cnt + 1);
+#ifndef GV_NO_PREFETCH
                 const uint2 i01 = *(const uint2*)((const u8*)hs + REC_IN_OFF);  // the predecessor's first two in-slots (inline position)
                 if (g.nunits) pf_l2((const u8*)hs + 64);                        // its out-slots, for when it is popped
+#endif
                 hs->cnt = (int)k;
                 ready = k == (sdeg >> 16);
                 if (ready) hs->best = NIL;
+#ifndef GV_NO_PREFETCH
                 if (sdeg & 0xFFFFu) gv_prefetch_rec(g, i01.x);
                 if ((sdeg & 0xFFFFu) > 1) gv_prefetch_rec(g, i01.y);
+#endif
             }
             __syncwarp();
             m2_queue_append(g, __ballot_sync(FULLMASK, ready), ready, s, tail, lane);
