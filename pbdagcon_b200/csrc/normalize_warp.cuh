@@ -20,7 +20,12 @@
 #define NW_TR 1024u  // raw columns normalised per tile: 32 per lane
 #define NW_MG 256u   // look-ahead margin staged behind the tile: 8 per lane
 #define NW_W (NW_TR + NW_MG)
+#ifndef NW_WARPS
 #define NW_WARPS 4
+#endif
+#ifndef NW_MIN_BLOCKS
+#define NW_MIN_BLOCKS 7
+#endif
 #define NW_STG 66u   // u16 per lane in the output staging area: 64 columns + padding against bank conflicts
 #define AF_RETRY 2u  // needs the serial kernel (look-ahead left the staged window)
 
@@ -122,7 +127,7 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, u32 lane) {
     return v;
 }
 
-__global__ void __launch_bounds__(NW_WARPS * 32, 7) k_normalize_warp(NormArgs a) {
+__global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp(NormArgs a) {
     __shared__ NwSmem sm_all[NW_WARPS];
     const u32 lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const u32 ai = a.aln_first + blockIdx.x * NW_WARPS + wid;

@@ -5,6 +5,7 @@
 //   AlnProvider                reference src/cpp/AlnProvider.hpp:32-46
 //   BlasrM5AlnProvider         reference src/cpp/BlasrM5AlnProvider.hpp (m5 and 'pre' text, grouped by target)
 //   ProgramOpts                reference src/cpp/ProgramOpts.hpp:8-36
+//   SimpleAligner              reference src/cpp/SimpleAligner.hpp (the -a step; arithmetic builder-written, see simple_align.cpp)
 // and replaces the Reader -> BoundedBuffer -> N x Consensus -> BoundedBuffer -> Writer thread pipeline
 // (reference src/cpp/main.cpp:37-176,248-274) with: one scanner thread that cuts the input text into
 // target groups, N packer threads that parse those lines straight into pinned dgc_batch buffers, and one
@@ -83,6 +84,11 @@ bool split_line(const char* p, size_t n, TextFormat fmt, LineFields& out);
 bool line_target_id(const char* p, size_t n, TextFormat fmt, const char*& id, size_t& id_len);
 // revComp of reference Alignment.cpp:15-26: complements upper-case ACGT only, then reverses.
 void revcomp_into(const char* src, size_t n, uint8_t* dst);
+// The `-a` arithmetic (simple_align.cpp): aligns the ungapped query segment q[0..qn) to the ungapped target segment
+// t[0..tn) and writes the gapped strings.  The result is local: it starts and ends on a matching column and covers the
+// target bases [t_begin, t_end) of the segment.  False when nothing aligns.
+bool simple_align(const char* q, size_t qn, const char* t, size_t tn, std::string& qout, std::string& tout,
+                  uint32_t& t_begin, uint32_t& t_end);
 
 // A packed batch in host memory (pinned when `pinned`), laid out as include/dagcon_b200.h: dgc_batch.
 class HostBatch {
@@ -157,6 +163,15 @@ typedef void (*BatchSink)(const HostBatch& batch, void* user);
 int pack_text(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err);
 
 }  // namespace dgh
+
+// Reference src/cpp/SimpleAligner.hpp: re-aligns one 'pre' record in place (gapped strings, start/end moved to the
+// aligned span, '-' strand records reverse-complemented into target orientation, start made 1-based).  Returns false
+// (and empties the strings) when nothing aligns; the reference has no such case because blasr always returns blocks.
+class SimpleAligner {
+public:
+    bool align(dagcon::Alignment& aln);
+    void operator()(dagcon::Alignment& aln) { align(aln); }
+};
 
 // Reference-shaped provider over the same line parser (m5 by default, 'pre' when asked).
 class BlasrM5AlnProvider : public AlnProvider {

@@ -111,6 +111,20 @@ int dgh_parse_line(const char* line, uint64_t n, int fmt, uint32_t* tlen, uint32
 }
 void dgh_free(void* p) { free(p); }
 
+// SimpleAligner::align on one 'pre' record (reference test/cpp/SimpleAlignerTest.cpp:8-21 drives it this way).
+// Returns 1 and malloc'd gapped strings (dgh_free), or 0 when nothing aligns.
+int dgh_simple_align(const char* q, const char* t, char strand, uint32_t tlen, uint32_t* start, uint32_t* end, char** qout,
+                     char** tout) {
+    dagcon::Alignment a;
+    a.tlen = tlen; a.start = *start; a.end = *end; a.strand = strand; a.qstr = q; a.tstr = t;
+    SimpleAligner sa;
+    if (!sa.align(a)) return 0;
+    *start = a.start; *end = a.end;
+    *qout = strdup(a.qstr.c_str());
+    *tout = strdup(a.tstr.c_str());
+    return 1;
+}
+
 // The reference-shaped provider: number of alignments per nextTarget() call, in call order (first call yields 0).
 // Returns the number of calls made (<= cap) or -1 on error.
 int dgh_provider_groups(const char* path, int fmt, uint32_t* sizes, int cap) {

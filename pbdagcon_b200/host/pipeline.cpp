@@ -346,11 +346,6 @@ int pack_text(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, 
 
 int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err) {
     const auto t0 = std::chrono::steady_clock::now();
-    if (opts.align) {
-        err = "-a (re-align 'pre' records before consensus) needs the blasr SDPAlign/GuidedAlign step whose source is not "
-              "part of the reference tree; this build accepts gapped m5 input only";
-        return DGC_E_INVALID;
-    }
     int ndev = dgc_device_count();
     if (ndev <= 0) {
         err = "no CUDA device: the consensus path runs on the GPU only (there is no CPU fallback)";

@@ -194,6 +194,25 @@ void HostBatch::add_target_lines(const std::vector<std::pair<const char*, size_t
     for (const auto& ln : lines) {
         LineFields f;
         if (!split_line(ln.first, ln.second, fmt, f)) continue;
+        std::string aq, at;  // 'pre' records are ungapped segments: align first (reference main.cpp:127-129)
+        if (fmt == TextFormat::PRE) {
+            uint32_t tb = 0, te = 0;
+            if (!simple_align(f.q, f.q_len, f.t, f.t_len, aq, at, tb, te)) continue;
+            // SimpleAligner.cpp:49-61
+            f.start += tb;
+            f.end = f.start + te;
+            if (f.strand == '-') {
+                f.start = f.tlen - f.end;
+                std::string rq(aq.size(), '\0'), rt(at.size(), '\0');
+                revcomp_into(aq.data(), aq.size(), (uint8_t*)&rq[0]);
+                revcomp_into(at.data(), at.size(), (uint8_t*)&rt[0]);
+                aq.swap(rq);
+                at.swap(rt);
+            }
+            f.start++;
+            f.q = aq.data(); f.q_len = aq.size();
+            f.t = at.data(); f.t_len = at.size();
+        }
         if (f.q_len != f.t_len) throw M5Exception::FormatError{"query and target alignment strings differ in length"};
         if (f.q_len > 0x7FFFFFFFull) throw M5Exception::FormatError{"alignment too long"};
         if (first) {

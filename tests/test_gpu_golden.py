@@ -147,3 +147,73 @@ def test_cli_tiny_batches_do_not_deadlock(api, tmp_path):
         assert r.returncode == 0, r.stderr
         outs.add(r.stdout)
     assert len(outs) == 1 and next(iter(outs)).count(">") >= 240
+
+
+def _pre_workload(seed, n_targets, L, n_reads):
+    """'pre' records as m4topre.py:205-206 writes them (ungapped query and target segments; '-' records carry both
+    segments reverse-complemented, coordinates on the reverse strand) plus the true targets."""
+    import random
+    from test_simple_align_cpu import mutate, revcomp
+    rng = random.Random(seed)
+    lines, truth = [], {}
+    for ti in range(n_targets):
+        tgt = bytes(rng.choice(b"ACGT") for _ in range(L))
+        tid = f"pre/{ti}/0_{L}"
+        truth[tid] = tgt
+        for r in range(n_reads):
+            span = rng.randint(int(0.5 * L), L)
+            s = rng.randint(0, L - span)
+            seg = tgt[s:s + span]
+            q = mutate(rng, seg, 0.15)
+            if r % 2:
+                lines.append(f"r{ti}_{r} {tid} - {L} {L - (s + span)} {L - s} {revcomp(q).decode()} {revcomp(seg).decode()}")
+            else:
+                lines.append(f"r{ti}_{r} {tid} + {L} {s} {s + span} {q.decode()} {seg.decode()}")
+    return lines, truth
+
+
+def test_cli_align_first_on_pre_records(api, tmp_path):
+    """`pbdagcon -a x.pre`: the host aligner turns ungapped 'pre' records into alignments and the CUDA
+    path corrects them.  The consensus must (1) equal what the reference binary prints for the SAME alignments written
+    as m5 (where oracle/_ref travelled) and (2) be close to the true target (reads carry 15 % errors)."""
+    import ctypes as C
+    from test_simple_align_cpu import align
+    L, n_targets, n_reads = 3000, 24, 24
+    lines, truth = _pre_workload(11, n_targets, L, n_reads)
+    pre = str(tmp_path / "x.pre")
+    open(pre, "w").write("\n".join(lines) + "\n")
+    out = run_cli(["-a", "-c", "8", "-j", "4"], pre)
+    recs = out.strip().split("\n")
+    assert len(recs) >= 2 * n_targets
+    # (2) close to the truth
+    for i in range(0, len(recs), 2):
+        tid = recs[i][1:].rsplit("/", 1)[0]
+        b, e = map(int, recs[i].rsplit("/", 1)[1].split("_"))
+        cns = recs[i + 1].encode()
+        tgt = truth[tid]
+        assert 0.6 * L <= len(cns) <= 1.05 * L          # the ends stay below -c 8 and are cut
+        # k-mer containment as an alignment-free identity bound (the reference binary reaches >= 99.5 % on this input)
+        kt = {tgt[j:j + 12] for j in range(len(tgt) - 11)}
+        hit = sum(cns[j:j + 12] in kt for j in range(len(cns) - 11))
+        assert hit >= 0.97 * (len(cns) - 11), (tid, hit, len(cns))
+    # (1) the same alignments as m5 through the reference binary
+    if not os.path.exists(helpers.REF_BIN):
+        pytest.skip("oracle/_ref/pbdagcon_ref did not travel: consensus-vs-truth checked only")
+    h = C.CDLL(os.path.join(ROOT, "pbdagcon_b200", "host", "libdagcon_host.so"))
+    h.dgh_simple_align.restype = C.c_int
+    h.dgh_simple_align.argtypes = [C.c_char_p, C.c_char_p, C.c_char, C.c_uint32, C.POINTER(C.c_uint32),
+                                   C.POINTER(C.c_uint32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+    h.dgh_free.argtypes = [C.c_void_p]
+    m5 = str(tmp_path / "x.m5")
+    with open(m5, "w") as f:
+        for ln in lines:
+            sid, tid, strand, tlen, s, e, q, t = ln.split(" ")
+            r = align(h, q.encode(), t.encode(), strand.encode(), int(tlen), int(s), int(e))
+            assert r is not None
+            qs, ts, start, _ = r
+            # strings are in target orientation already: write a '+' record, 0-based start (Alignment.cpp:57-79)
+            f.write(f"{sid} 0 0 0 + {tid} {tlen} {start - 1} 0 + 0 0 0 0 0 0 {qs.decode()} | {ts.decode()}\n")
+    ref = subprocess.run([helpers.REF_BIN, "-j", "4", "-c", "8", m5], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                         text=True, timeout=300)
+    assert ref.returncode == 0
+    assert canon(out) == canon(ref.stdout)
