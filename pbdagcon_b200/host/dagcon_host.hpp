@@ -99,6 +99,8 @@ public:
     HostBatch& operator=(const HostBatch&) = delete;
 
     void clear();
+    // Capacity for what is about to be added (one allocation instead of doubling).
+    void reserve(size_t arena_need, size_t alns, size_t targets);
     // Appends one target given its lines.  All lines must carry the same target id.
     void add_target_lines(const std::vector<std::pair<const char*, size_t>>& lines, TextFormat fmt);
     // Appends one target from provider output (the reference-facing form).
@@ -141,8 +143,8 @@ struct ProgramOpts {
     std::string input = "-";
     // dispatcher
     int gpus = 0;           // 0 = all visible devices
-    size_t batchTargets = 1024;
-    size_t batchBytes = 512ull << 20;
+    size_t batchTargets = 256;          // a batch closes at this many targets or this much input text: small enough
+    size_t batchBytes = 192ull << 20;   // that several are being packed at once and the page-locked ring stays small
     bool stats = false;
 };
 

@@ -19,6 +19,9 @@
 #include <mutex>
 #include <thread>
 
+#include <sys/mman.h>
+#include <sys/stat.h>
+
 #include "dagcon_host.hpp"
 
 namespace dgh {
@@ -27,6 +30,9 @@ namespace {
 struct Block {
     std::unique_ptr<char[]> buf;
     size_t cap = 0, len = 0;
+    void* map = nullptr;  // a regular input file is mapped whole instead of being read into blocks
+    size_t map_len = 0;
+    ~Block() { if (map) munmap(map, map_len); }
 };
 
 struct WorkUnit {
@@ -95,8 +101,9 @@ public:
             fd = open(o_.input.c_str(), O_RDONLY);
             if (fd < 0) throw M5Exception::FileOpenError();
         }
-        auto blk = new_block(BLOCK_BYTES);
         unit_.reset(new WorkUnit());
+        if (fd > 0 && run_mapped(fd)) return;
+        auto blk = new_block(BLOCK_BYTES);
         bool eof = false;
         while (!eof) {
             while (blk->len < blk->cap) {  // fill the block
@@ -134,6 +141,33 @@ public:
     }
 
 private:
+    // A regular file: one read-only mapping, scanned in place (no read() copy, no fresh pages to fault in); the
+    // work units keep the mapping alive through their block lists.
+    bool run_mapped(int fd) {
+        struct stat sb;
+        if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode) || sb.st_size <= 0) return false;
+        const size_t len = (size_t)sb.st_size;
+        void* m = mmap(nullptr, len, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (m == MAP_FAILED) return false;
+        madvise(m, len, MADV_SEQUENTIAL);
+        auto blk = std::make_shared<Block>();
+        blk->map = m;
+        blk->map_len = blk->len = blk->cap = len;
+        close(fd);
+        st_.input_bytes += len;
+        const char* line = (const char*)m;
+        const char* e = line + len;
+        while (line < e) {
+            const char* nl = (const char*)memchr(line, '\n', (size_t)(e - line));
+            if (!nl) { take_line(blk, line, (size_t)(e - line)); break; }  // last line without '\n'
+            take_line(blk, line, (size_t)(nl - line));
+            line = nl + 1;
+        }
+        close_target();
+        flush_unit();
+        return true;
+    }
+
     std::shared_ptr<Block> new_block(size_t cap) {
         auto b = std::make_shared<Block>();
         b->buf.reset(new char[cap]);
@@ -258,8 +292,7 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
             std::lock_guard<std::mutex> lk(pool_mu);
             if (pool_made < pool_max) {
                 pool_made++;
-                const size_t acap = std::min<size_t>(o.batchBytes + (o.batchBytes >> 3), 8ull << 30);
-                hb.reset(new HostBatch(pinned, acap, 64 * o.batchTargets, o.batchTargets + 1));
+                hb.reset(new HostBatch(pinned, 0, 0, 0));  // sized by the packer once it holds its unit
                 return true;
             }
         }
@@ -296,6 +329,10 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                     try {
                         hb->clear();
                         hb->seq = u->seq;
+                        // m5 lines carry the two strings plus a match pattern of the same length; aligned 'pre'
+                        // strings grow by their gaps (a low guess only costs one doubling)
+                        hb->reserve((fmt == TextFormat::M5 ? u->bytes * 2 / 3 : u->bytes + u->bytes / 4) + 64 * u->lines.size(),
+                                    u->lines.size(), u->targets());
                         std::vector<std::pair<const char*, size_t>> lines;
                         for (size_t t = 0; t + 1 < u->tgt_begin.size(); t++) {
                             lines.assign(u->lines.begin() + u->tgt_begin[t], u->lines.begin() + u->tgt_begin[t + 1]);
@@ -344,6 +381,10 @@ int pack_text(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, 
     return fr.rc;
 }
 
+static double since(std::chrono::steady_clock::time_point t0) {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
 int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err) {
     const auto t0 = std::chrono::steady_clock::now();
     int ndev = dgc_device_count();
@@ -354,7 +395,7 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
     const int G = opts.gpus > 0 ? std::min(opts.gpus, ndev) : ndev;
     // the reader and the packers start at once: scanning the text overlaps the CUDA context and handle creation
     Front fr(opts, true, stats);
-    fr.start((size_t)G * DGC_MAX_INFLIGHT + 2);
+    fr.start((size_t)G * DGC_MAX_INFLIGHT + 4);
     std::vector<dgc_handle*> hs((size_t)G, nullptr);
     auto destroy_all = [&] { for (auto h : hs) if (h) dgc_destroy(h); };
     for (int g = 0; g < G; g++) {
@@ -363,6 +404,7 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         const int rc = dgc_create(&o, &hs[(size_t)g]);
         if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); fr.stop(); destroy_all(); return rc; }
     }
+    if (opts.verbose) fprintf(stderr, "pbdagcon-b200: %.3f s %d GPU handle(s) ready\n", since(t0), G);
 
     std::deque<std::unique_ptr<HostBatch>> inflight;  // in submit (= input) order; batch k runs on GPU k % G
     std::vector<int> on_gpu((size_t)G, 0);
@@ -376,6 +418,7 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         dgc_results r{};
         const int c = dgc_collect(hs[(size_t)g], &r);
         on_gpu[(size_t)g]--;
+        if (opts.verbose) fprintf(stderr, "pbdagcon-b200: %.3f s collected batch %llu\n", since(t0), (unsigned long long)hb->seq);
         if (c) {
             if (!rc) { rc = c; err = std::string("dgc_collect: ") + dgc_last_error(hs[(size_t)g]); }
         } else if (!rc) {
@@ -412,6 +455,7 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         while (on_gpu[(size_t)g] >= DGC_MAX_INFLIGHT) collect_oldest();
         const dgc_batch b = hb->view();
         // the dgc_batch struct is read during submit only; the arrays it points to stay alive in `inflight`
+        if (opts.verbose) fprintf(stderr, "pbdagcon-b200: %.3f s submit batch %llu (%u targets, %.1f MB) to GPU %d\n", since(t0), (unsigned long long)seq, hb->n_targets, hb->arena_bytes / 1e6, g);
         const int c = dgc_submit(hs[(size_t)g], &b);
         if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); fr.recycle(std::move(hb)); continue; }
         on_gpu[(size_t)g]++;

@@ -157,12 +157,18 @@ static void grow(HostBatch* hb, T*& p, size_t used, size_t new_cap, void* (HostB
 
 void HostBatch::need_arena(size_t extra) {
     if (arena_bytes + extra <= arena_cap_) return;
-    size_t nc = std::max(arena_cap_ * 2, (size_t)arena_bytes + extra);
+    // an empty batch is sized to what its unit needs (page-locking is paid per byte); a filling one doubles
+    size_t nc = arena_bytes ? std::max(arena_cap_ * 2, (size_t)arena_bytes + extra) : extra + (extra >> 4);
     uint8_t* np = (uint8_t*)alloc(nc);
     memcpy(np, arena, arena_bytes);
     release(arena);
     arena = np;
     arena_cap_ = nc;
+}
+void HostBatch::reserve(size_t arena_need, size_t alns, size_t targets) {
+    need_arena(arena_need);
+    need_alns(alns);
+    need_targets(targets);
 }
 void HostBatch::need_alns(size_t extra) {
     if (n_alns + extra <= aln_cap_) return;
