@@ -12,7 +12,7 @@
 //
 // Method: global DP inside a band around the scaled diagonal (row i of the query is centred on column i*m/n of the
 // target), widened by doubling until the optimal path keeps clear of the band's edges; the traceback prefers the
-// diagonal, so gaps in homopolymer runs land leftmost.  O(n * band) time and bytes.
+// diagonal, so gaps in homopolymer runs land leftmost.  O(n * band) time and bytes (at most 256 MB per thread).
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -104,8 +104,11 @@ bool simple_align(const char* q, size_t qn, const char* t, size_t tn, std::strin
     if (qn == 0 || tn == 0) return false;
     const int64_t n = (int64_t)qn, m = (int64_t)tn, full = std::max(n, m) + 1;
     bool ok = false;
+    // the traceback matrix is held to 256 MB per packer thread: the widest band that fits is the last one tried, and
+    // on it a path along the band's edge is accepted (unrelated sequences end there instead of in a full n x m matrix)
+    constexpr int64_t kMaxCells = 256ll << 20;
     for (int64_t band = 64;; band *= 2) {
-        const bool last = band >= full;
+        const bool last = band >= full || (n + 1) * (4 * band + 1) > kMaxCells;
         ok = banded_pass(q, n, t, m, std::min(band, full), s, last);
         if (ok || last) break;
     }

@@ -111,3 +111,16 @@ def test_band_widens_for_long_indels(host):
 def test_nothing_to_align(host):
     assert align(host, b"AAAAAAAA", b"CCCCCCCC", b"+", 100, 1, 9) is None
     assert align(host, b"", b"ACGT", b"+", 100, 1, 5) is None
+
+
+def test_unrelated_sequences_stay_bounded(host):
+    # no band is ever clear of the path here: the search must stop at the widest band its memory bound allows and
+    # still hand back a well-formed (if meaningless) alignment, or nothing
+    rng = random.Random(99)
+    q = bytes(rng.choice(b"ACGT") for _ in range(6000))
+    t = bytes(rng.choice(b"ACGT") for _ in range(5000))
+    r = align(host, q, t, b"+", 9000, 1, 5001)
+    if r is not None:
+        qs, ts, start, end = r
+        assert len(qs) == len(ts)
+        assert qs.replace(b"-", b"") in q and ts.replace(b"-", b"") in t
