@@ -90,6 +90,15 @@ void revcomp_into(const char* src, size_t n, uint8_t* dst);
 bool simple_align(const char* q, size_t qn, const char* t, size_t tn, std::string& qout, std::string& tout,
                   uint32_t& t_begin, uint32_t& t_end);
 
+// One 'pre' record after the -a step (text_input.cpp: align_pre_line).
+struct PreAligned {
+    bool ok = false;      // false: blank line, or nothing aligns (the record is dropped)
+    uint32_t start = 0;   // 1-based, target orientation
+    std::string q, t;     // gapped strings, target orientation
+};
+// False on a blank line; throws M5Exception::FormatError like split_line.
+bool align_pre_line(const char* p, size_t n, PreAligned& out);
+
 // A packed batch in host memory (pinned when `pinned`), laid out as include/dagcon_b200.h: dgc_batch.
 class HostBatch {
 public:
@@ -102,7 +111,8 @@ public:
     // Capacity for what is about to be added (one allocation instead of doubling).
     void reserve(size_t arena_need, size_t alns, size_t targets);
     // Appends one target given its lines.  All lines must carry the same target id.
-    void add_target_lines(const std::vector<std::pair<const char*, size_t>>& lines, TextFormat fmt);
+    // `pre` (optional, 'pre' format only): the lines' alignments, computed by the caller (in parallel).
+    void add_target_lines(const std::vector<std::pair<const char*, size_t>>& lines, TextFormat fmt, const PreAligned* pre = nullptr);
     // Appends one target from provider output (the reference-facing form).
     void add_target(const std::vector<dagcon::Alignment>& alns, const std::string* backbone = nullptr);
     dgc_batch view() const;

@@ -10,6 +10,7 @@
 #include <unistd.h>
 #include <fcntl.h>
 
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <cstring>
@@ -299,9 +300,35 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
         return free_batches.pop(hb);
     }
 
+    // -a: the alignments of one unit, by `-j` threads at once (a unit may be the whole input; the DP is the cost)
+    void align_unit(const WorkUnit& u, std::vector<PreAligned>& out) {
+        out.resize(u.lines.size());
+        std::atomic<size_t> next{0};
+        std::mutex mu;
+        std::string first_err;
+        auto work = [&] {
+            for (size_t i; (i = next.fetch_add(1)) < u.lines.size();) {
+                try {
+                    align_pre_line(u.lines[i].first, u.lines[i].second, out[i]);
+                } catch (const M5Exception::FormatError& e) {
+                    std::lock_guard<std::mutex> lk(mu);
+                    if (first_err.empty()) first_err = e.msg;
+                    next.store(u.lines.size());
+                }
+            }
+        };
+        std::vector<std::thread> pool;
+        for (int i = 1; i < std::max(1, o.threads); i++) pool.emplace_back(work);
+        work();
+        for (auto& t : pool) t.join();
+        if (!first_err.empty()) throw M5Exception::FormatError{first_err};
+    }
+
     void start(size_t pool) {
         pool_max = pool;
-        const int np = std::max(1, o.threads);
+        // with -a a unit's alignments already use every thread: two packers, so that the next unit is aligned while
+        // this one is packed and submitted
+        const int np = fmt == TextFormat::PRE ? 2 : std::max(1, o.threads);
         live_packers = np;
         threads.emplace_back([this] {
             const auto t0 = std::chrono::steady_clock::now();
@@ -333,10 +360,12 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                         // strings grow by their gaps (a low guess only costs one doubling)
                         hb->reserve((fmt == TextFormat::M5 ? u->bytes * 2 / 3 : u->bytes + u->bytes / 4) + 64 * u->lines.size(),
                                     u->lines.size(), u->targets());
+                        std::vector<PreAligned> aligned;
+                        if (fmt == TextFormat::PRE) align_unit(*u, aligned);
                         std::vector<std::pair<const char*, size_t>> lines;
                         for (size_t t = 0; t + 1 < u->tgt_begin.size(); t++) {
                             lines.assign(u->lines.begin() + u->tgt_begin[t], u->lines.begin() + u->tgt_begin[t + 1]);
-                            hb->add_target_lines(lines, fmt);
+                            hb->add_target_lines(lines, fmt, aligned.empty() ? nullptr : &aligned[u->tgt_begin[t]]);
                         }
                     } catch (const M5Exception::FormatError& e) { fail(DGC_E_INVALID, "Format error. Input: " + o.input + ", Error: " + e.msg);
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); }

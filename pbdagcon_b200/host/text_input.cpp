@@ -193,31 +193,47 @@ void HostBatch::need_targets(size_t extra) {
 
 static inline uint64_t align16(uint64_t x) { return (x + 15) & ~15ull; }
 
-void HostBatch::add_target_lines(const std::vector<std::pair<const char*, size_t>>& lines, TextFormat fmt) {
+// One 'pre' line through the -a step: ungapped segments in, gapped strings in target orientation out
+// (reference main.cpp:127-129 -> SimpleAligner.cpp:25-63).
+bool align_pre_line(const char* p, size_t n, PreAligned& out) {
+    LineFields f;
+    out.ok = false;
+    if (!split_line(p, n, TextFormat::PRE, f)) return false;
+    uint32_t tb = 0, te = 0;
+    if (!simple_align(f.q, f.q_len, f.t, f.t_len, out.q, out.t, tb, te)) return true;  // parsed, nothing aligns
+    // SimpleAligner.cpp:49-61
+    f.start += tb;
+    f.end = f.start + te;
+    if (f.strand == '-') {
+        f.start = f.tlen - f.end;
+        std::string rq(out.q.size(), '\0'), rt(out.t.size(), '\0');
+        revcomp_into(out.q.data(), out.q.size(), (uint8_t*)&rq[0]);
+        revcomp_into(out.t.data(), out.t.size(), (uint8_t*)&rt[0]);
+        out.q.swap(rq);
+        out.t.swap(rt);
+    }
+    out.start = f.start + 1;
+    out.ok = true;
+    return true;
+}
+
+void HostBatch::add_target_lines(const std::vector<std::pair<const char*, size_t>>& lines, TextFormat fmt, const PreAligned* pre) {
     need_targets(1);
     need_alns(lines.size());
     bool first = true;
+    PreAligned local;
+    size_t li = 0;
     for (const auto& ln : lines) {
+        const size_t idx = li++;
         LineFields f;
         if (!split_line(ln.first, ln.second, fmt, f)) continue;
-        std::string aq, at;  // 'pre' records are ungapped segments: align first (reference main.cpp:127-129)
-        if (fmt == TextFormat::PRE) {
-            uint32_t tb = 0, te = 0;
-            if (!simple_align(f.q, f.q_len, f.t, f.t_len, aq, at, tb, te)) continue;
-            // SimpleAligner.cpp:49-61
-            f.start += tb;
-            f.end = f.start + te;
-            if (f.strand == '-') {
-                f.start = f.tlen - f.end;
-                std::string rq(aq.size(), '\0'), rt(at.size(), '\0');
-                revcomp_into(aq.data(), aq.size(), (uint8_t*)&rq[0]);
-                revcomp_into(at.data(), at.size(), (uint8_t*)&rt[0]);
-                aq.swap(rq);
-                at.swap(rt);
-            }
-            f.start++;
-            f.q = aq.data(); f.q_len = aq.size();
-            f.t = at.data(); f.t_len = at.size();
+        if (fmt == TextFormat::PRE) {  // 'pre' records are ungapped segments: aligned first (by the caller, or here)
+            const PreAligned* a = pre ? &pre[idx] : &local;
+            if (!pre) align_pre_line(ln.first, ln.second, local);
+            if (!a->ok) continue;
+            f.start = a->start;
+            f.q = a->q.data(); f.q_len = a->q.size();
+            f.t = a->t.data(); f.t_len = a->t.size();
         }
         if (f.q_len != f.t_len) throw M5Exception::FormatError{"query and target alignment strings differ in length"};
         if (f.q_len > 0x7FFFFFFFull) throw M5Exception::FormatError{"alignment too long"};
