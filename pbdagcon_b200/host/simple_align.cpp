@@ -25,6 +25,7 @@ namespace {
 
 constexpr int32_t kMatch = -5, kMismatch = 6, kIns = 4, kDel = 5;  // SimpleAligner.cpp:10-23
 constexpr int32_t kInf = 1 << 29;
+constexpr int64_t G0 = 4;  // guard cells on each side of a DP row
 
 struct Scratch {
     std::vector<uint8_t> tb;
@@ -38,45 +39,52 @@ inline int64_t centre(int64_t i, int64_t n, int64_t m) { return n ? (i * m) / n 
 // (the caller widens the band); on success `s.q`/`s.t` hold the gapped strings REVERSED.
 bool banded_pass(const char* q, int64_t n, const char* t, int64_t m, int64_t band, Scratch& s, bool final_pass) {
     const int64_t W = 2 * band + 1;
+    constexpr int64_t G = G0;  // guard cells (kept at kInf) on both sides of a row: no index checks in the inner loop
     s.tb.assign((size_t)((n + 1) * W), 0);
-    s.prev.assign((size_t)W, kInf);
-    s.cur.assign((size_t)W, kInf);
+    s.prev.assign((size_t)(W + 2 * G), kInf);
+    s.cur.assign((size_t)(W + 2 * G), kInf);
     for (int64_t k = 0; k < W; k++) {
         const int64_t j = centre(0, n, m) - band + k;
-        if (j >= 0 && j <= m) { s.prev[(size_t)k] = (int32_t)(j * kDel); s.tb[(size_t)k] = 2; }
+        if (j >= 0 && j <= m) { s.prev[(size_t)(k + G)] = (int32_t)(j * kDel); s.tb[(size_t)k] = 2; }
     }
     for (int64_t i = 1; i <= n; i++) {
         const int64_t c1 = centre(i, n, m), sh = c1 - centre(i - 1, n, m);
         uint8_t* tbr = s.tb.data() + (size_t)(i * W);
         const char qc = q[i - 1];
-        for (int64_t k = 0; k < W; k++) {
-            const int64_t j = c1 - band + k;
-            int32_t best = kInf;
-            uint8_t dir = 0;
-            if (j >= 0 && j <= m) {
-                const int64_t kd = k + sh - 1, ku = k + sh;  // (i-1, j-1) and (i-1, j) in the previous row
-                if (j >= 1 && kd >= 0 && kd < W && s.prev[(size_t)kd] < kInf) {
-                    const int32_t v = s.prev[(size_t)kd] + (qc == t[j - 1] ? kMatch : kMismatch);
-                    if (v < best) { best = v; dir = 1; }
-                }
-                if (j >= 1 && k >= 1 && s.cur[(size_t)k - 1] < kInf) {  // (i, j-1): target base against '-'
-                    const int32_t v = s.cur[(size_t)k - 1] + kDel;
-                    if (v < best) { best = v; dir = 2; }
-                }
-                if (ku >= 0 && ku < W && s.prev[(size_t)ku] < kInf) {  // (i-1, j): query base against '-'
-                    const int32_t v = s.prev[(size_t)ku] + kIns;
-                    if (v < best) { best = v; dir = 3; }
-                }
-            }
-            s.cur[(size_t)k] = best;
-            tbr[k] = dir;
+        int32_t* cur = s.cur.data() + G;
+        const int32_t* prev = s.prev.data() + G;
+        // columns j = c1 - band + k inside [0, m]
+        const int64_t klo = std::max<int64_t>(0, band - c1), khi = std::min<int64_t>(W - 1, m - c1 + band);
+        for (int64_t k = 0; k < klo && k < W; k++) { cur[k] = kInf; tbr[k] = 0; }
+        for (int64_t k = std::max<int64_t>(khi + 1, 0); k < W; k++) { cur[k] = kInf; tbr[k] = 0; }
+        int64_t k = klo;
+        if (k <= khi && c1 - band + k == 0) {  // column 0: only (i-1, 0) leads here
+            const int64_t ku = k + sh;
+            const int32_t v = (ku < W + G) ? prev[ku] + kIns : kInf;
+            cur[k] = v < kInf ? v : kInf;
+            tbr[k] = v < kInf ? 3 : 0;
+            k++;
+        }
+        if (sh > G - 1) return false;  // a target more than 3x the query: not an alignment this band can hold
+        const int64_t tj = c1 - band - 1;  // t[j - 1] = t[tj + k]
+        for (; k <= khi; k++) {
+            const int32_t vd = prev[k + sh - 1] + (qc == t[tj + k] ? kMatch : kMismatch);  // (i-1, j-1)
+            const int32_t vl = cur[k - 1] + kDel;                                       // (i, j-1): target base against '-'
+            const int32_t vu = prev[k + sh] + kIns;                                     // (i-1, j): query base against '-'
+            int32_t best = vd;
+            uint8_t dir = 1;
+            if (vl < best) { best = vl; dir = 2; }
+            if (vu < best) { best = vu; dir = 3; }
+            const bool dead = best >= kInf;
+            cur[k] = dead ? kInf : best;
+            tbr[k] = dead ? (uint8_t)0 : dir;
         }
         s.prev.swap(s.cur);
     }
     int64_t i = n, j = m;
     {
         const int64_t k = j - (centre(i, n, m) - band);
-        if (k < 0 || k >= W || s.prev[(size_t)k] >= kInf) return false;
+        if (k < 0 || k >= W || s.prev[(size_t)(k + G0)] >= kInf) return false;
     }
     s.q.clear();
     s.t.clear();
