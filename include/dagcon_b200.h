@@ -57,7 +57,7 @@ typedef struct dgc_opts {
     uint32_t trim;          /* -t: target bases trimmed from both alignment ends */
     uint32_t flags;         /* DGC_F_* */
     int32_t device;         /* CUDA device ordinal */
-    uint32_t targets_per_warp; /* serial graph kernels: 0 = auto */
+    uint32_t reserved0;     /* must be 0 (was targets_per_warp; the sweeps are always one warp per target) */
     uint64_t scratch_bytes; /* HBM budget for the per-chunk graph arena; 0 = default (112 GiB: 10 000 targets of 8 kb x 30x or 4 800 of 20 kb x 50x in one chunk) */
 } dgc_opts;
 

@@ -28,7 +28,7 @@ class DagconError(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("min_cov", C.c_uint32), ("min_len", C.c_uint32), ("trim", C.c_uint32), ("flags", C.c_uint32),
-                ("device", C.c_int32), ("targets_per_warp", C.c_uint32), ("scratch_bytes", C.c_uint64)]
+                ("device", C.c_int32), ("reserved0", C.c_uint32), ("scratch_bytes", C.c_uint64)]
 
 
 class CBatch(C.Structure):
@@ -211,9 +211,9 @@ class Results:
 class Consensus:
     """One GPU's consensus engine.  Mirrors ProgramOpts (-c min_cov, -m/-l min_len, -t trim)."""
 
-    def __init__(self, min_cov=6, min_len=500, trim=50, flags=0, device=0, targets_per_warp=0, scratch_bytes=0):
+    def __init__(self, min_cov=6, min_len=500, trim=50, flags=0, device=0, scratch_bytes=0):
         self.lib = load_library()
-        o = Opts(min_cov, min_len, trim, flags, device, targets_per_warp, scratch_bytes)
+        o = Opts(min_cov, min_len, trim, flags, device, 0, scratch_bytes)
         h = C.c_void_p()
         rc = self.lib.dgc_create(C.byref(o), C.byref(h))
         if rc != 0:

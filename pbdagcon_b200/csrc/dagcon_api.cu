@@ -37,15 +37,17 @@ struct DevBuf {
         if (e == cudaSuccess) cap = want;
         return e;
     }
-    // grow without losing the first `live` bytes (device-wide sync: only taken when an estimate fell short)
-    cudaError_t ensure_keep(size_t bytes, size_t live) {
+    // Grow without losing the first `live` bytes.  `st` is the stream whose kernels wrote those bytes: the copy is
+    // enqueued behind them on that stream and has finished before the old buffer is freed (the slot streams are
+    // cudaStreamNonBlocking, so a copy on the legacy default stream would NOT be ordered after them).
+    cudaError_t ensure_keep(size_t bytes, size_t live, cudaStream_t st) {
         if (bytes <= cap) return cudaSuccess;
         void* np = nullptr;
         const size_t want = bytes + bytes / 4 + 256;
         cudaError_t e = cudaMalloc(&np, want);
         if (e != cudaSuccess) return e;
-        if (p && live) e = cudaMemcpy(np, p, std::min(live, cap), cudaMemcpyDeviceToDevice);
-        else e = cudaDeviceSynchronize();
+        if (p && live) e = cudaMemcpyAsync(np, p, std::min(live, cap), cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
         if (p) cudaFree(p);
         p = np; cap = want;
         return e;
@@ -196,12 +198,13 @@ int validate_batch(const dgc_batch* b, std::string& err) {
         for (uint32_t t = 0; t < b->n_targets; t++) {
             if (b->tgt_aln_begin[t + 1] < b->tgt_aln_begin[t]) { err = "tgt_aln_begin not monotone"; return DGC_E_INVALID; }
             if (b->tgt_tlen[t] > 0x3FFFFFFFu) { err = "tlen too large"; return DGC_E_INVALID; }
-            if (b->tgt_bb_off && b->tgt_bb_off[t] + b->tgt_tlen[t] > b->arena_bytes) { err = "backbone outside arena"; return DGC_E_INVALID; }
+            if (b->tgt_bb_off && (b->tgt_bb_off[t] > b->arena_bytes || b->tgt_tlen[t] > b->arena_bytes - b->tgt_bb_off[t])) { err = "backbone outside arena"; return DGC_E_INVALID; }
         }
     } else if (b->n_alns) { err = "alignments without targets"; return DGC_E_INVALID; }
     for (uint32_t k = 0; k < b->n_alns; k++) {
         uint64_t n = b->aln_len[k];
-        if (b->aln_q_off[k] + n > b->arena_bytes || b->aln_t_off[k] + n > b->arena_bytes) {
+        if (b->aln_q_off[k] > b->arena_bytes || n > b->arena_bytes - b->aln_q_off[k] || b->aln_t_off[k] > b->arena_bytes ||
+            n > b->arena_bytes - b->aln_t_off[k]) {
             err = "alignment string outside arena"; return DGC_E_INVALID;
         }
     }
@@ -298,7 +301,11 @@ int launch_plan(Slot& s, const dgc_dbatch& db, uint32_t t0, uint32_t t1) {
 }
 
 struct Chunk { uint32_t first, count; uint64_t nUnits, nPos, nCons, nFrag, nGs; uint32_t maxL2; };
-uint64_t chunk_bytes(const Chunk& c) { return 128 * c.nUnits + 9 * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; }
+// per-position accumulators of the build (gacc): sized for the wide (u16 list length) variant, 11 bytes per position;
+// every target's share is rounded up to 16 positions so that the u16 arrays inside stay aligned whatever L is
+constexpr uint64_t ACC_BYTES = 11;
+inline uint64_t pos16(uint64_t L2) { return (L2 + 15) & ~15ull; }
+uint64_t chunk_bytes(const Chunk& c) { return 128 * c.nUnits + ACC_BYTES * c.nPos + c.nCons + 8 * c.nFrag + 4 * c.nGs; }
 
 // Pool of list blocks behind a target's records, in 8-byte words (a multiple of 16 keeps every arena 128-byte
 // aligned): enter's out-list and exit's in-list always, the rest only when a list outgrows its record.  The normal
@@ -328,14 +335,21 @@ int launch_build(Slot& s, dgc_dbatch& db, uint32_t first, uint32_t count, uint32
     ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>();
     ba.rec = s.rec.as<u8>();
     ba.tgt_status_out = s.t_status.as<u32>(); ba.tgt_nv = s.t_nv.as<u32>(); ba.tgt_pool_top = s.t_pool_top.as<u32>();
-    // per-position running sums: 9 B per position in shared memory when the longest backbone of the chunk fits
+    // List lengths per position are bytes unless a target of the launch has so many alignments that a backbone vertex
+    // could collect 254 edges (A + 1 >= 254): then the u16 variant runs (11 instead of 9 bytes per position).
+    uint32_t maxA = 0;
+    for (uint32_t t = first; t < first + count; t++) maxA = std::max(maxA, db.h_aln_begin[t + 1] - db.h_aln_begin[t]);
+    const bool wide = maxA + 2 >= acc_max_deg<u8>();
+    const uint64_t bpp = wide ? acc_bytes_per_pos<u16>() : acc_bytes_per_pos<u8>();
+    // per-position running sums in shared memory when the longest backbone of the chunk fits
     // (a launch whose longest backbone does not fit asks for no dynamic shared memory at all: the accumulators of all
     // its targets go to `gacc`, which stays L2-resident, and the blocks per SM are no longer limited by shared memory)
-    ba.smem_positions = 9ull * maxL2 <= h->build_smem_max ? maxL2 : 0;
+    ba.smem_positions = bpp * maxL2 <= h->build_smem_max ? maxL2 : 0;
     ba.gacc = s.gacc.as<u8>();
-    const size_t build_smem = (9ull * ba.smem_positions + 15) & ~15ull;
+    const size_t build_smem = (bpp * ba.smem_positions + 15) & ~15ull;
     span_begin(s, PH_BUILD);
-    k_build_graph2<<<count, BT, build_smem, st>>>(ba);
+    if (wide) k_build_graph2<u16><<<count, BT, build_smem, st>>>(ba);
+    else k_build_graph2<u8><<<count, BT, build_smem, st>>>(ba);
     s.tm.launches++;
     CU(cudaGetLastError());
     span_end(s);
@@ -494,7 +508,7 @@ int retry_pool_failures(Slot& s, dgc_dbatch& db, int stop_after) {
             const uint64_t units = L2 + V + pcap / 16;
             if (16 * units > 0xFFFFFFF0ull || pcap > 0xFFFFFFF0ull) break;  // stays T_POOL -> reported as DGC_T_INTERNAL
             Chunk nxt = c;
-            nxt.nUnits += units; nxt.nPos += L2; nxt.nCons += (V + 15) & ~15ull; nxt.nFrag += p_fcap[t]; nxt.nGs += p_gcap[t]; nxt.count++;
+            nxt.nUnits += units; nxt.nPos += pos16(L2); nxt.nCons += (V + 15) & ~15ull; nxt.nFrag += p_fcap[t]; nxt.nGs += p_gcap[t]; nxt.count++;
             if (chunk_bytes(nxt) > budget) break;
             p_rec[t] = c.nUnits; p_pos[t] = c.nPos; p_cons[t] = c.nCons; p_frag[t] = c.nFrag; p_gs[t] = c.nGs;
             p_pcap[t] = (uint32_t)pcap;
@@ -506,7 +520,7 @@ int retry_pool_failures(Slot& s, dgc_dbatch& db, int stop_after) {
         const size_t a = c.first, n = c.count;
         CU(s.rec.ensure(128 * c.nUnits + 256));
         CU(s.cons.ensure(c.nCons + 64)); CU(s.frags.ensure(8 * c.nFrag + 64)); CU(s.gscratch.ensure(4 * c.nGs + 64));
-        if (9ull * c.maxL2 > h->build_smem_max) CU(s.gacc.ensure(9 * c.nPos + 64));
+        if (ACC_BYTES * c.maxL2 > h->build_smem_max) CU(s.gacc.ensure(ACC_BYTES * c.nPos + 64));
         CU(cudaMemcpyAsync(s.rec_off.as<u64>() + a, p_rec + a, 8 * n, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(s.pos_off.as<u64>() + a, p_pos + a, 8 * n, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(s.cons_off.as<u64>() + a, p_cons + a, 8 * n, cudaMemcpyHostToDevice, st));
@@ -594,14 +608,14 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         if (16 * units > 0xFFFFFFF0ull) { s.err = "one target's graph exceeds the 32 GiB a list pointer can address"; return DGC_E_NOMEM; }
         if (chunk_bytes(one) > budget) { s.err = "one target needs more than scratch_bytes of graph arena"; return DGC_E_NOMEM; }
         Chunk nxt = cur;
-        nxt.nUnits += units; nxt.nPos += L2; nxt.nCons += consb; nxt.nFrag += fcap; nxt.nGs += gcap; nxt.count++;
+        nxt.nUnits += units; nxt.nPos += pos16(L2); nxt.nCons += consb; nxt.nFrag += fcap; nxt.nGs += gcap; nxt.count++;
         if (cur.count && (chunk_bytes(nxt) > budget || cur.count >= (1u << 20))) {
             chunks.push_back(cur);
             cur = Chunk{(uint32_t)t, 0, 0, 0, 0, 0, 0, 0};
         }
         p_rec[t] = cur.nUnits; p_pos[t] = cur.nPos; p_cons[t] = cur.nCons; p_frag[t] = cur.nFrag; p_gs[t] = cur.nGs;
         p_fcap[t] = (uint32_t)fcap; p_gcap[t] = (uint32_t)gcap; p_pcap[t] = (uint32_t)pcap;
-        cur.nUnits += units; cur.nPos += L2; cur.nCons += consb; cur.nFrag += fcap; cur.nGs += gcap; cur.count++;
+        cur.nUnits += units; cur.nPos += pos16(L2); cur.nCons += consb; cur.nFrag += fcap; cur.nGs += gcap; cur.count++;
         cur.maxL2 = std::max(cur.maxL2, (uint32_t)L2);
         out_cons_cap += V; out_frag_cap += fcap;
         s.tm.nodes += V; s.tm.norm_cols += ok ? hp_cols[t] : 0;
@@ -614,12 +628,12 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         mUnits = std::max(mUnits, c.nUnits); mPos = std::max(mPos, c.nPos);
         mCons = std::max(mCons, c.nCons); mFrag = std::max(mFrag, c.nFrag); mGs = std::max(mGs, c.nGs);
         s.tm.arena_bytes += chunk_bytes(c);
-        if (9ull * c.maxL2 > h->build_smem_max) need_gacc = true;
+        if (ACC_BYTES * c.maxL2 > h->build_smem_max) need_gacc = true;
     }
     s.tm.chunks = (uint32_t)chunks.size();
     CU(s.rec.ensure(128 * mUnits + 256));
     CU(s.cons.ensure(mCons + 64)); CU(s.frags.ensure(8 * mFrag + 64)); CU(s.gscratch.ensure(4 * mGs + 64));
-    if (need_gacc) CU(s.gacc.ensure(9 * mPos + 64));
+    if (need_gacc) CU(s.gacc.ensure(ACC_BYTES * mPos + 64));
     CU(s.out_cons.ensure(out_cons_cap + 64)); CU(s.out_frags.ensure(8 * out_frag_cap + 64));
     CU(cudaMemcpyAsync(s.rec_off.p, p_rec, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.pos_off.p, p_pos, 8 * T, cudaMemcpyHostToDevice, st));
@@ -775,13 +789,13 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
     // does chunk c fit the arenas as they are allocated now?
     auto cap_ok = [&](const Chunk& c) {
         return 128 * c.nUnits + 256 <= s.rec.cap && c.nCons + 64 <= s.cons.cap && 8 * c.nFrag + 64 <= s.frags.cap &&
-               4 * c.nGs + 64 <= s.gscratch.cap && (9ull * c.maxL2 <= h->build_smem_max || 9 * c.nPos + 64 <= s.gacc.cap);
+               4 * c.nGs + 64 <= s.gscratch.cap && (ACC_BYTES * c.maxL2 <= h->build_smem_max || ACC_BYTES * c.nPos + 64 <= s.gacc.cap);
     };
     // (re)allocate the chunk arenas for c; only while no chunk is open (cudaFree waits for the kernels still using them)
     auto cap_ensure = [&](const Chunk& c) -> int {
         CU(s.rec.ensure(128 * c.nUnits + 256));
         CU(s.cons.ensure(c.nCons + 64)); CU(s.frags.ensure(8 * c.nFrag + 64)); CU(s.gscratch.ensure(4 * c.nGs + 64));
-        if (9ull * c.maxL2 > h->build_smem_max) CU(s.gacc.ensure(9 * c.nPos + 64));
+        if (ACC_BYTES * c.maxL2 > h->build_smem_max) CU(s.gacc.ensure(ACC_BYTES * c.nPos + 64));
         return DGC_OK;
     };
     auto flush_build = [&]() -> int {
@@ -807,8 +821,8 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
     auto close_chunk = [&]() -> int {
         int r = flush_build();
         if (r || !cur.count) return r;
-        CU(s.out_cons.ensure_keep(out_cons_need + 64, live_cons));
-        CU(s.out_frags.ensure_keep(8 * out_frag_need + 64, 8 * live_frag));
+        CU(s.out_cons.ensure_keep(out_cons_need + 64, live_cons, st));
+        CU(s.out_frags.ensure_keep(8 * out_frag_need + 64, 8 * live_frag, st));
         live_cons = out_cons_need; live_frag = out_frag_need;
         r = launch_serial(s, db, cur, 2);
         s.tm.arena_bytes += chunk_bytes(cur);
@@ -850,11 +864,11 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
             const uint64_t units = ok ? L2 + V + pcap / 16 : 0;
             const uint64_t fcap = ok ? V / ((uint64_t)o.min_len + 1) + 2 : 0, gcap = ok ? 8ull * (A + 2) + 64 : 0;
             Chunk& n = need[i];
-            n.nUnits = units; n.nPos = L2; n.nCons = (V + 15) & ~15ull; n.nFrag = fcap; n.nGs = gcap; n.maxL2 = (uint32_t)L2;
+            n.nUnits = units; n.nPos = pos16(L2); n.nCons = (V + 15) & ~15ull; n.nFrag = fcap; n.nGs = gcap; n.maxL2 = (uint32_t)L2;
             if (16 * units > 0xFFFFFFF0ull) { s.err = "one target's graph exceeds the 32 GiB a list pointer can address"; return DGC_E_NOMEM; }
             if (chunk_bytes(n) > budget) { s.err = "one target needs more than scratch_bytes of graph arena"; return DGC_E_NOMEM; }
             p_fcap[t] = (uint32_t)fcap; p_gcap[t] = (uint32_t)gcap; p_pcap[t] = (uint32_t)pcap;
-            sum.nUnits += units; sum.nPos += L2; sum.nCons += n.nCons; sum.nFrag += fcap; sum.nGs += gcap;
+            sum.nUnits += units; sum.nPos += pos16(L2); sum.nCons += n.nCons; sum.nFrag += fcap; sum.nGs += gcap;
             sum.maxL2 = std::max(sum.maxL2, n.maxL2);
             piece_cons += V; piece_frag += fcap;
             s.tm.nodes += V; s.tm.norm_cols += ok ? hp_cols[t] : 0;
@@ -887,8 +901,8 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
             }
             const uint64_t oc = (uint64_t)((out_cons_need + piece_cons) + piece_cons * (scale - 1.0));
             const uint64_t of = (uint64_t)((out_frag_need + piece_frag) + piece_frag * (scale - 1.0));
-            CU(s.out_cons.ensure_keep(oc + 64, live_cons));
-            CU(s.out_frags.ensure_keep(8 * of + 64, 8 * live_frag));
+            CU(s.out_cons.ensure_keep(oc + 64, live_cons, st));
+            CU(s.out_frags.ensure_keep(8 * of + 64, 8 * live_frag, st));
         }
         // ---- arena offsets target by target; a chunk closes when the next target does not fit
         for (size_t i = 0; i < nT; i++) {
@@ -1045,7 +1059,8 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
         // 74 KB = three blocks per SM.  Measured on B200: 8 kb backbones 89 ms in shared memory vs 103 ms in gacc;
         // 20 kb backbones 184 ms in shared memory (180 KB, one block per SM) vs 114 ms in gacc
         optin = std::min<size_t>(optin, 74 * 1024);
-        if (cudaFuncSetAttribute(k_build_graph2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)optin) == cudaSuccess)
+        if (cudaFuncSetAttribute(k_build_graph2<u8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)optin) == cudaSuccess &&
+            cudaFuncSetAttribute(k_build_graph2<u16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)optin) == cudaSuccess)
             h->build_smem_max = optin;
         else { cudaGetLastError(); h->build_smem_max = 40 * 1024; }
     }

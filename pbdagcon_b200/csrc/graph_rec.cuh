@@ -226,15 +226,22 @@ struct Build2Args {
     u8* gacc;  // 9 bytes per position
 };
 
+// DT = type of the per-position list lengths: u8 (9 bytes per position; a backbone vertex has at most A + 1 in- or
+// out-edges, so this is exact for targets of up to 252 alignments) or u16 (11 bytes per position; any target the
+// 16-bit degrees of the records can hold, i.e. up to 65 000 alignments).  The dispatcher picks the variant per launch.
+template <typename DT>
 struct BuildAcc {  // per-position running state of the replay
     u16* cov;
     u16* w;
     u16* c;
     u8* b;
-    u8* dout;
-    u8* din;
+    DT* dout;
+    DT* din;
 };
+template <typename DT> __host__ __device__ constexpr u32 acc_max_deg() { return sizeof(DT) == 1 ? 254u : 65534u; }
+template <typename DT> __host__ __device__ constexpr u32 acc_bytes_per_pos() { return 7u + 2u * (u32)sizeof(DT); }
 
+template <typename DT>
 struct B2Ctx {
     u8* base;
     u32 L, A, nbb, enter_out, exit_in, pool_end;  // enter_out / exit_in: word index of slot 0 of the two wide lists
@@ -242,25 +249,27 @@ struct B2Ctx {
     u32* s_status;
     u32* s_enter_out;
     u32* s_exit_in;
-    BuildAcc acc;
+    BuildAcc<DT> acc;
 };
-__device__ __forceinline__ Hdr* b2_hdr(const B2Ctx& c, u32 h) { return (Hdr*)(c.base + (size_t)h * REC_UNIT); }
+template <typename DT>
+__device__ __forceinline__ Hdr* b2_hdr(const B2Ctx<DT>& c, u32 h) { return (Hdr*)(c.base + (size_t)h * REC_UNIT); }
 
 // append (p -> dst handle, count 1) to backbone vertex p's out-list
-__device__ __forceinline__ void b2_append_out(const B2Ctx& c, u32 p, u32 dsth) {
+template <typename DT>
+__device__ __forceinline__ void b2_append_out(const B2Ctx<DT>& c, u32 p, u32 dsth) {
     u32 n, ptr;
     if (p == 0) {
         n = (*c.s_enter_out)++;
         ptr = c.enter_out;
     } else {
         n = c.acc.dout[p];
-        if (n >= 254u) { *c.s_status = T_TOO_MANY; return; }
-        c.acc.dout[p] = (u8)(n + 1);
+        if (n >= acc_max_deg<DT>()) { *c.s_status = T_TOO_MANY; return; }
+        c.acc.dout[p] = (DT)(n + 1);
         ptr = n <= BB_OUT_CAP ? gv_inline_out(2 * p) : b2_hdr(c, 2 * p)->out_ptr;
         const u32 have = n <= BB_OUT_CAP ? BB_OUT_CAP : (u32)((const u64*)c.base)[ptr - 1];
         if (n == have) {  // full: the list moves into a pool block twice the size (a backbone vertex has at most A+1 out-edges)
             const u32 cap = min(2u * have, max(c.A + 2, have + 1)), blk = atomicAdd(c.s_pool_top, cap + 1);
-            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.dout[p] = (u8)n; return; }
+            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.dout[p] = (DT)n; return; }
             ((u64*)c.base)[blk] = cap;
             const OSlot* o = (const OSlot*)(c.base + (size_t)ptr * 8);
             OSlot* no = (OSlot*)(c.base + (size_t)(blk + 1) * 8);
@@ -273,20 +282,21 @@ __device__ __forceinline__ void b2_append_out(const B2Ctx& c, u32 p, u32 dsth) {
     s.dst = dsth; s.cv = 1;
     ((OSlot*)(c.base + (size_t)ptr * 8))[n] = s;
 }
-__device__ __forceinline__ void b2_append_in(const B2Ctx& c, u32 p, u32 srch) {
+template <typename DT>
+__device__ __forceinline__ void b2_append_in(const B2Ctx<DT>& c, u32 p, u32 srch) {
     u32 n, ptr;
     if (p == c.L + 1) {
         n = (*c.s_exit_in)++;
         ptr = c.exit_in;
     } else {
         n = c.acc.din[p];
-        if (n >= 254u) { *c.s_status = T_TOO_MANY; return; }
-        c.acc.din[p] = (u8)(n + 1);
+        if (n >= acc_max_deg<DT>()) { *c.s_status = T_TOO_MANY; return; }
+        c.acc.din[p] = (DT)(n + 1);
         ptr = n <= REC_IN_CAP ? gv_inline_in(2 * p) : b2_hdr(c, 2 * p)->in_ptr;
         const u32 have = n <= REC_IN_CAP ? REC_IN_CAP : (u32)((const u64*)c.base)[ptr - 1];
         if (n == have) {
             const u32 cap = min(2u * have, max(c.A + 2, have + 1)), words = (cap + 1) / 2, blk = atomicAdd(c.s_pool_top, words + 1);
-            if (blk + words + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.din[p] = (u8)n; return; }
+            if (blk + words + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.din[p] = (DT)n; return; }
             ((u64*)c.base)[blk] = cap;
             const u32* in = (const u32*)(c.base + (size_t)ptr * 8);
             u32* ni = (u32*)(c.base + (size_t)(blk + 1) * 8);
@@ -300,7 +310,8 @@ __device__ __forceinline__ void b2_append_in(const B2Ctx& c, u32 p, u32 srch) {
 
 // addEdge(prev, cur) (:109-127) for one path step; prev/cur are vertex ids.  An insertion vertex on the path was
 // created by the alignment being replayed: its single in-slot / out-slot is written directly.
-__device__ __forceinline__ void b2_edge(const B2Ctx& c, u32 prev, u32 cur) {
+template <typename DT>
+__device__ __forceinline__ void b2_edge(const B2Ctx<DT>& c, u32 prev, u32 cur) {
     const u32 nbb = c.nbb;
     const bool prev_bb = prev < nbb, cur_bb = cur < nbb;
     const u32 ph = gv_handle(prev, nbb), ch = gv_handle(cur, nbb);
@@ -325,6 +336,7 @@ __device__ __forceinline__ void b2_edge(const B2Ctx& c, u32 prev, u32 cur) {
 #ifndef BUILD_MIN_BLOCKS
 #define BUILD_MIN_BLOCKS 3  // 40 registers: three 512-thread blocks per SM also when no shared memory limits them (gacc)
 #endif
+template <typename DT>
 __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Args a) {
     const u32 t = a.first + blockIdx.x;
     if (a.tgt_status[t] != T_OK) return;
@@ -335,14 +347,21 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
     __shared__ u32 sa[BT / 32], sb[BT / 32], s_cur[TILE];
     __shared__ u32 s_pool_top, s_status, s_enter_out, s_exit_in;
     extern __shared__ __align__(16) u8 s_dyn[];
-    u8* accbase = (nbb <= a.smem_positions) ? s_dyn : a.gacc + 9ull * a.acc_off[t];
-    B2Ctx c;
+    // acc_off[t] is a multiple of 16 positions (the planner rounds every target up), so both layouts stay aligned
+    u8* accbase = (nbb <= a.smem_positions) ? s_dyn : a.gacc + (u64)acc_bytes_per_pos<DT>() * a.acc_off[t];
+    B2Ctx<DT> c;
     c.acc.cov = (u16*)accbase;
     c.acc.w = c.acc.cov + nbb;
     c.acc.c = c.acc.w + nbb;
-    c.acc.b = (u8*)(c.acc.c + nbb);
-    c.acc.dout = c.acc.b + nbb;
-    c.acc.din = c.acc.dout + nbb;
+    if (sizeof(DT) == 2) {
+        c.acc.dout = (DT*)(c.acc.c + nbb);
+        c.acc.din = c.acc.dout + nbb;
+        c.acc.b = (u8*)(c.acc.din + nbb);
+    } else {
+        c.acc.b = (u8*)(c.acc.c + nbb);
+        c.acc.dout = (DT*)(c.acc.b + nbb);
+        c.acc.din = c.acc.dout + nbb;
+    }
     c.base = a.rec + (size_t)REC_UNIT * a.rec_off[t];
     c.L = L; c.A = a1 - a0; c.nbb = nbb;
     const u32 pool_begin = 16u * (nbb + a.tgt_V[t]);

@@ -421,7 +421,10 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         err = "no CUDA device: the consensus path runs on the GPU only (there is no CPU fallback)";
         return DGC_E_NODEVICE;
     }
-    const int G = opts.gpus > 0 ? std::min(opts.gpus, ndev) : ndev;
+    // DGC_SHARE_GPUS=1: --gpus N may exceed the visible devices; handle g then drives device g % ndev.  Lets a one-GPU
+    // box exercise the round-robin dealing and the ordered gather of the multi-GPU dispatcher (tests).
+    const bool share = getenv("DGC_SHARE_GPUS") && getenv("DGC_SHARE_GPUS")[0] == '1';
+    const int G = opts.gpus > 0 ? (share ? opts.gpus : std::min(opts.gpus, ndev)) : ndev;
     // the reader and the packers start at once: scanning the text overlaps the CUDA context and handle creation
     Front fr(opts, true, stats);
     fr.start((size_t)G * DGC_MAX_INFLIGHT + 4);
@@ -429,7 +432,7 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
     auto destroy_all = [&] { for (auto h : hs) if (h) dgc_destroy(h); };
     for (int g = 0; g < G; g++) {
         dgc_opts o{};
-        o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = g;
+        o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = g % ndev;
         const int rc = dgc_create(&o, &hs[(size_t)g]);
         if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); fr.stop(); destroy_all(); return rc; }
     }

@@ -230,10 +230,17 @@ void HostBatch::add_target_lines(const std::vector<std::pair<const char*, size_t
         if (fmt == TextFormat::PRE) {  // 'pre' records are ungapped segments: aligned first (by the caller, or here)
             const PreAligned* a = pre ? &pre[idx] : &local;
             if (!pre) align_pre_line(ln.first, ln.second, local);
-            if (!a->ok) continue;
-            f.start = a->start;
-            f.q = a->q.data(); f.q_len = a->q.size();
-            f.t = a->t.data(); f.t_len = a->t.size();
+            if (a->ok) {
+                f.start = a->start;
+                f.q = a->q.data(); f.q_len = a->q.size();
+                f.t = a->t.data(); f.t_len = a->t.size();
+            } else {
+                // Nothing aligns: the record still counts towards the target's alignment count (the reference tests
+                // alns.size() before it aligns, main.cpp:66-72,118) and is then dropped by the raw minLen filter
+                // (main.cpp:132): packed as a zero-column alignment.
+                f.start += 1;
+                f.q_len = f.t_len = 0;
+            }
         }
         if (f.q_len != f.t_len) throw M5Exception::FormatError{"query and target alignment strings differ in length"};
         if (f.q_len > 0x7FFFFFFFull) throw M5Exception::FormatError{"alignment too long"};

@@ -135,6 +135,12 @@ def have_ref():
     return os.path.exists(REF_SO)
 
 
+def checker():
+    """The strongest checker available: the compiled reference (oracle/_ref travels to the GPU box) when it was
+    built, else the C restatement.  Same consensus()/normalize_trim() interface either way."""
+    return Ref() if have_ref() else Oracle()
+
+
 # ------------------------------------------------------------------ python-side fuzz generators
 def rand_target(rng: random.Random, L=None, n_aln=None, err=0.15, full=False, alphabet="ACGT", dots=False,
                 min_span=20):

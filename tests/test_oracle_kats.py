@@ -54,3 +54,16 @@ def test_raw_consensus_kat(name):
     ]
     r = c.consensus(9, alns, backbone=b"ATATTAGGC", mode=MODE_MERGE | MODE_SINGLE, min_weight=0)
     assert r["single"] == b"ATATAGCCGGC"
+
+
+def test_bgl_shim_selftest(tmp_path):
+    """oracle/shim's Boost.Graph stand-in against the documented vecS/vecS/bidirectionalS rules every tie-break of the
+    reference rests on (append order, parallel edges, edge(u,v) first match, order-preserving clear_vertex, dense ids)."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "shim_selftest")
+    subprocess.run(["g++", "-std=c++14", "-O1", "-I" + os.path.join(root, "oracle", "shim"), "-o", exe,
+                    os.path.join(root, "oracle", "shim_selftest.cpp")], check=True)
+    r = subprocess.run([exe], stdout=subprocess.PIPE, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "shim ok", r.stdout
