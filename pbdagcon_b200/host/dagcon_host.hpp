@@ -14,6 +14,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <exception>
+#include <functional>
+#include <memory>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -151,6 +154,13 @@ struct ProgramOpts {
     bool align = false;     // -a: input is 'pre' and must be aligned first
     bool verbose = false;
     std::string input = "-";
+    // dazcon (reference src/cpp/ProgramOpts.hpp:24-35)
+    std::string alnFile;            // -a: the daligner .las file
+    std::string seqFile;            // -s: the DAZZ_DB .db
+    unsigned int maxHits = 85;      // -m
+    bool sortCov = false;           // -x
+    bool properOvls = false;        // -o
+    std::set<int> targets;          // positional: limit consensus to these (1-based) target ids
     // dispatcher
     int gpus = 0;           // 0 = all visible devices
     size_t batchTargets = 256;          // a batch closes at this many targets or this much input text: small enough
@@ -168,10 +178,25 @@ struct RunStats {
 // in input-target order.  Returns 0 or a DGC_E_* code (message in `err`).
 int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err);
 
+// Where the dispatcher gets its packed batches from (the text front or the dazcon front), in input order.
+struct BatchFeed {
+    std::function<std::unique_ptr<HostBatch>(uint64_t seq)> take;   // nullptr = stream finished
+    std::function<void(std::unique_ptr<HostBatch>)> recycle;
+    std::function<bool()> failed;
+};
+int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunStats& stats, std::string& err, bool dazcon_header);
+
+// dazcon: reads the DAZZ_DB `opts.seqFile` and the LAS `opts.alnFile`, rebuilds every selected overlap's alignment
+// from its trace points, runs every target through the GPUs and writes ">id/n/b_e\nSEQ\n" records to `out`
+// (reference src/cpp/dazcon.cpp:38-120).
+int run_daz_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err);
+// The dazcon front alone (scanner + realignment workers): every packed batch goes to `sink` in input order.
+typedef void (*BatchSink)(const HostBatch& batch, void* user);
+int pack_daz(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err);
+
 // The scanner stage alone, for tests and for callers that bring their own dispatcher: cuts the text into
 // batches of whole targets and hands each packed batch to `sink` in input order (sink owns nothing; the
 // batch is recycled after it returns).
-typedef void (*BatchSink)(const HostBatch& batch, void* user);
 int pack_text(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err);
 
 }  // namespace dgh
@@ -183,6 +208,21 @@ class SimpleAligner {
 public:
     bool align(dagcon::Alignment& aln);
     void operator()(dagcon::Alignment& aln) { align(aln); }
+};
+
+// Reference src/cpp/DazAlnProvider.hpp:144-184: the targets of a daligner LAS file (the A reads, in file order) with
+// the alignments of their best hits, rebuilt from the trace points (daz_provider.cpp).  Dazzler types stay behind
+// the implementation pointer; the dazzler C library (DALIGNER align.c, DAZZ_DB DB.c/QV.c) is linked as it is.
+class DazAlnProvider : public AlnProvider {
+public:
+    explicit DazAlnProvider(const dgh::ProgramOpts& popts);   // throws PacBio::DagCon::IOException
+    ~DazAlnProvider() override;
+    bool nextTarget(std::vector<dagcon::Alignment>& dest) override;
+    bool nextTarget(std::string& targSeq, std::vector<dagcon::Alignment>& dest) override;
+
+private:
+    struct Impl;
+    std::unique_ptr<Impl> impl_;
 };
 
 // Reference-shaped provider over the same line parser (m5 by default, 'pre' when asked).

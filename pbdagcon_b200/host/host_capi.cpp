@@ -12,7 +12,7 @@ namespace {
 
 struct Packed {  // every batch the scanner produced, concatenated
     std::vector<uint32_t> tgt_tlen, tgt_aln_begin{0}, aln_start, aln_len, batch_targets;
-    std::vector<uint64_t> aln_q_off, aln_t_off;
+    std::vector<uint64_t> aln_q_off, aln_t_off, tgt_bb_off;
     std::vector<uint8_t> arena;
     std::string ids;  // '\n'-separated
     dgh::RunStats st;
@@ -33,6 +33,7 @@ void sink(const dgh::HostBatch& b, void* user) {
     }
     for (uint32_t t = 0; t < b.n_targets; t++) {
         p.tgt_tlen.push_back(b.tgt_tlen[t]);
+        if (b.has_backbone) p.tgt_bb_off.push_back(base + b.tgt_bb_off[t]);
         p.tgt_aln_begin.push_back(a0 + b.tgt_aln_begin[t + 1]);
         p.ids += b.ids[t];
         p.ids.push_back('\n');
@@ -55,6 +56,22 @@ void* dgh_pack_file(const char* path, int fmt, uint32_t min_cov, int threads, ui
     if (rc && p->err.empty()) p->err = "pack_text failed";
     return p;
 }
+#ifdef DGH_HAVE_DAZ
+// The dazcon front over a DB + LAS pair: every target with its backbone and the alignments rebuilt from the trace
+// points, packed as the C ABI takes them (same handle type as dgh_pack_file; array 9 = tgt_bb_off).
+void* dgh_pack_daz(const char* db, const char* las, uint32_t min_cov, uint32_t max_hits, int sort_cov, int proper, int threads,
+                   uint32_t batch_targets, double* seconds) {
+    Packed* p = new Packed();
+    dgh::ProgramOpts o;
+    o.seqFile = db; o.alnFile = las; o.minCov = min_cov; o.maxHits = max_hits; o.sortCov = sort_cov != 0; o.properOvls = proper != 0;
+    o.threads = threads;
+    if (batch_targets) o.batchTargets = batch_targets;
+    const int rc = dgh::pack_daz(o, false, sink, p, p->st, p->err);
+    if (rc && p->err.empty()) p->err = "pack_daz failed";
+    if (seconds) *seconds = p->st.seconds;
+    return p;
+}
+#endif
 const char* dgh_pack_error(void* h) { return ((Packed*)h)->err.c_str(); }
 uint32_t dgh_pack_counts(void* h, int which) {
     Packed* p = (Packed*)h;
@@ -80,6 +97,7 @@ const void* dgh_pack_array(void* h, int which) {
         case 6: return p->arena.data();
         case 7: return p->ids.c_str();
         case 8: return p->batch_targets.data();
+        case 9: return p->tgt_bb_off.empty() ? nullptr : p->tgt_bb_off.data();
         default: return nullptr;
     }
 }

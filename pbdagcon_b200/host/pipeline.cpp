@@ -24,6 +24,7 @@
 #include <sys/stat.h>
 
 #include "dagcon_host.hpp"
+#include "channels.hpp"
 
 namespace dgh {
 namespace {
@@ -43,50 +44,6 @@ struct WorkUnit {
     std::vector<uint32_t> tgt_begin{0};  // CSR over lines
     size_t bytes = 0;
     size_t targets() const { return tgt_begin.size() - 1; }
-};
-
-template <class T>
-class Channel {  // bounded FIFO; close() wakes everybody
-public:
-    explicit Channel(size_t cap) : cap_(cap) {}
-    bool push(T v) {
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_space_.wait(lk, [&] { return q_.size() < cap_ || closed_; });
-        if (closed_) return false;
-        q_.push_back(std::move(v));
-        cv_item_.notify_one();
-        return true;
-    }
-    bool pop(T& v) {
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_item_.wait(lk, [&] { return !q_.empty() || closed_; });
-        if (q_.empty()) return false;
-        v = std::move(q_.front());
-        q_.pop_front();
-        cv_space_.notify_one();
-        return true;
-    }
-    bool try_pop(T& v) {
-        std::lock_guard<std::mutex> lk(mu_);
-        if (q_.empty()) return false;
-        v = std::move(q_.front());
-        q_.pop_front();
-        cv_space_.notify_one();
-        return true;
-    }
-    void close() {
-        std::lock_guard<std::mutex> lk(mu_);
-        closed_ = true;
-        cv_item_.notify_all();
-        cv_space_.notify_all();
-    }
-
-private:
-    std::mutex mu_;
-    std::condition_variable cv_item_, cv_space_;
-    std::deque<T> q_;
-    size_t cap_;
-    bool closed_ = false;
 };
 
 constexpr size_t BLOCK_BYTES = 64u << 20;
@@ -230,37 +187,7 @@ private:
     uint64_t next_seq_ = 0;
 };
 
-// Packed batches come out of the packers in any order; the dispatcher takes them by sequence number.
-class OrderedOutbox {
-public:
-    void put(std::unique_ptr<HostBatch> b) {
-        std::lock_guard<std::mutex> lk(mu_);
-        const uint64_t s = b->seq;
-        ready_[s] = std::move(b);
-        cv_.notify_all();
-    }
-    // nullptr when the stream is finished (or failed)
-    std::unique_ptr<HostBatch> take(uint64_t seq) {
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_.wait(lk, [&] { return ready_.count(seq) || done_; });
-        auto it = ready_.find(seq);
-        if (it == ready_.end()) return nullptr;
-        auto b = std::move(it->second);
-        ready_.erase(it);
-        return b;
-    }
-    void finish() {
-        std::lock_guard<std::mutex> lk(mu_);
-        done_ = true;
-        cv_.notify_all();
-    }
-
-private:
-    std::mutex mu_;
-    std::condition_variable cv_;
-    std::map<uint64_t, std::unique_ptr<HostBatch>> ready_;
-    bool done_ = false;
-};
+typedef OrderedOutboxT<HostBatch> OrderedOutbox;
 
 struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
     const ProgramOpts& o;
@@ -414,7 +341,11 @@ static double since(std::chrono::steady_clock::time_point t0) {
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
-int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err) {
+// The dispatcher proper, shared by the text front (pbdagcon) and the dazcon front: creates one handle per GPU, deals
+// the feed's batches round-robin (dgc_submit, <= DGC_MAX_INFLIGHT per GPU), collects in input order (dgc_collect) and
+// writes the FASTA records: ">id/b_e\nSEQ\n" (reference main.cpp:139-145) or, for dazcon, ">id/n/b_e\nSEQ\n" with
+// n the running record index in input order (= `dazcon -j 1`, reference dazcon.cpp:62,92-99).
+int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunStats& stats, std::string& err, bool dazcon_header) {
     const auto t0 = std::chrono::steady_clock::now();
     int ndev = dgc_device_count();
     if (ndev <= 0) {
@@ -425,23 +356,22 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
     // box exercise the round-robin dealing and the ordered gather of the multi-GPU dispatcher (tests).
     const bool share = getenv("DGC_SHARE_GPUS") && getenv("DGC_SHARE_GPUS")[0] == '1';
     const int G = opts.gpus > 0 ? (share ? opts.gpus : std::min(opts.gpus, ndev)) : ndev;
-    // the reader and the packers start at once: scanning the text overlaps the CUDA context and handle creation
-    Front fr(opts, true, stats);
-    fr.start((size_t)G * DGC_MAX_INFLIGHT + 4);
     std::vector<dgc_handle*> hs((size_t)G, nullptr);
     auto destroy_all = [&] { for (auto h : hs) if (h) dgc_destroy(h); };
     for (int g = 0; g < G; g++) {
         dgc_opts o{};
         o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = g % ndev;
         const int rc = dgc_create(&o, &hs[(size_t)g]);
-        if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); fr.stop(); destroy_all(); return rc; }
+        if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); destroy_all(); return rc; }
     }
-    if (opts.verbose) fprintf(stderr, "pbdagcon-b200: %.3f s %d GPU handle(s) ready\n", since(t0), G);
+    if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s %d GPU handle(s) ready\n", dazcon_header ? "dazcon" : "pbdagcon", since(t0), G);
 
     std::deque<std::unique_ptr<HostBatch>> inflight;  // in submit (= input) order; batch k runs on GPU k % G
     std::vector<int> on_gpu((size_t)G, 0);
     std::string text;
+    long long well = 0;
     int rc = 0;
+    const char* prog = dazcon_header ? "dazcon" : "pbdagcon";
 
     auto collect_oldest = [&]() {
         auto hb = std::move(inflight.front());
@@ -450,20 +380,21 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
         dgc_results r{};
         const int c = dgc_collect(hs[(size_t)g], &r);
         on_gpu[(size_t)g]--;
-        if (opts.verbose) fprintf(stderr, "pbdagcon-b200: %.3f s collected batch %llu\n", since(t0), (unsigned long long)hb->seq);
+        if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s collected batch %llu\n", prog, since(t0), (unsigned long long)hb->seq);
         if (c) {
             if (!rc) { rc = c; err = std::string("dgc_collect: ") + dgc_last_error(hs[(size_t)g]); }
         } else if (!rc) {
             text.clear();
             for (uint32_t t = 0; t < r.n_targets; t++) {
                 if (r.tgt_status[t] > DGC_T_SKIPPED)  // rejected, never silently: the reference would walk off its vertex array here
-                    fprintf(stderr, "pbdagcon: target %s rejected (status %u: %s)\n", hb->ids[t].c_str(), r.tgt_status[t],
+                    fprintf(stderr, "%s: target %s rejected (status %u: %s)\n", prog, hb->ids[t].c_str(), r.tgt_status[t],
                             r.tgt_status[t] == DGC_T_BAD_ALIGNMENT ? "an alignment runs off the backbone" :
                             r.tgt_status[t] == DGC_T_TOO_MANY_ALNS ? "too many alignments" : "internal");
                 for (uint32_t f = r.tgt_frag_begin[t]; f < r.tgt_frag_begin[t + 1]; f++) {
                     text.push_back('>');
                     text += hb->ids[t];
                     text.push_back('/');
+                    if (dazcon_header) { append_int(text, well++); text.push_back('/'); }
                     append_int(text, r.frag_range0[f]);
                     text.push_back('_');
                     append_int(text, r.frag_range1[f]);
@@ -476,28 +407,46 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
             }
             if (!text.empty() && fwrite(text.data(), 1, text.size(), out) != text.size()) { rc = DGC_E_INVALID; err = "write error on the FASTA output"; }
         }
-        fr.recycle(std::move(hb));
+        feed.recycle(std::move(hb));
     };
 
     for (uint64_t seq = 0;; seq++) {
-        auto hb = fr.outbox.take(seq);
+        auto hb = feed.take(seq);
         if (!hb) break;
-        if (rc || fr.rc) { fr.recycle(std::move(hb)); continue; }
+        if (rc || feed.failed()) { feed.recycle(std::move(hb)); continue; }
         const int g = (int)(seq % (uint64_t)G);
         while (on_gpu[(size_t)g] >= DGC_MAX_INFLIGHT) collect_oldest();
         const dgc_batch b = hb->view();
         // the dgc_batch struct is read during submit only; the arrays it points to stay alive in `inflight`
-        if (opts.verbose) fprintf(stderr, "pbdagcon-b200: %.3f s submit batch %llu (%u targets, %.1f MB) to GPU %d\n", since(t0), (unsigned long long)seq, hb->n_targets, hb->arena_bytes / 1e6, g);
+        if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s submit batch %llu (%u targets, %.1f MB) to GPU %d\n", prog, since(t0), (unsigned long long)seq, hb->n_targets, hb->arena_bytes / 1e6, g);
         const int c = dgc_submit(hs[(size_t)g], &b);
-        if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); fr.recycle(std::move(hb)); continue; }
+        if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); feed.recycle(std::move(hb)); continue; }
         on_gpu[(size_t)g]++;
         stats.batches++;
         inflight.push_back(std::move(hb));
     }
     while (!inflight.empty()) collect_oldest();
     fflush(out);
-    fr.stop();
     destroy_all();
+    return rc;
+}
+
+int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (dgc_device_count() <= 0) {
+        err = "no CUDA device: the consensus path runs on the GPU only (there is no CPU fallback)";
+        return DGC_E_NODEVICE;
+    }
+    // the reader and the packers start at once: scanning the text overlaps the CUDA context and handle creation
+    Front fr(opts, true, stats);
+    const int G = opts.gpus > 0 ? opts.gpus : std::max(1, dgc_device_count());
+    fr.start((size_t)G * DGC_MAX_INFLIGHT + 4);
+    BatchFeed feed;
+    feed.take = [&](uint64_t seq) { return fr.outbox.take(seq); };
+    feed.recycle = [&](std::unique_ptr<HostBatch> hb) { fr.recycle(std::move(hb)); };
+    feed.failed = [&] { return fr.rc != 0; };
+    int rc = dispatch_batches(opts, feed, out, stats, err, false);
+    fr.stop();
     if (!rc && fr.rc) { rc = fr.rc; err = fr.err; }
     stats.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return rc;
