@@ -1,5 +1,5 @@
 // daz_capi.cpp -- extern "C" hooks over the dazcon front so that tests (ctypes) can pin the host provider against the
-// reference's DazAlnProvider (oracle/_ref/libdaz_ref.so) and its TargetHit scoring (reference test/cpp/TargetHitTest.cpp).
+// reference's DazAlnProvider (built by the test infrastructure) and its TargetHit scoring (reference test/cpp/TargetHitTest.cpp).
 // No compute on the consensus path in here.
 #include <cstring>
 #include <string>
@@ -15,7 +15,7 @@ struct Dump { std::string text; };
 extern "C" {
 
 // Every (targSeq, alns) the provider yields, as text: "T id tlen nalns targSeq" then "A sid start qstr tstr" lines
-// (same format as oracle/daz_ref_capi.cpp: dazref_dump).
+// (the checker built from the reference prints the same format).
 void* dgh_daz_dump(const char* db, const char* las, unsigned min_cov, unsigned max_hits, int sort_cov, int proper,
                    const int* targets, int n_targets) {
     Dump* d = new Dump();
