@@ -11,7 +11,40 @@ DAZREF_SO = os.path.join(ROOT, "oracle", "_ref", "libdaz_ref.so")
 DAZCON = os.path.join(ROOT, "pbdagcon_b200", "host", "dazcon")
 DAZCON_REF = os.path.join(ROOT, "oracle", "_ref", "dazcon_ref")
 FIX = os.path.join(ROOT, "tests", "golden", "daz")
-DB, LAS = os.path.join(FIX, "small.db"), os.path.join(FIX, "small.las")
+_fixdir = None
+
+
+def fixture_paths():
+    """(db, las) of the committed fixture, laid out the way DAZZ_DB wants it: small.db next to its hidden companions
+    .small.idx / .small.bps (committed under visible names, copied into a scratch directory once per process)."""
+    global _fixdir
+    if _fixdir is None:
+        import atexit
+        import shutil
+        import tempfile
+        d = tempfile.mkdtemp(prefix="dgc_dazfix_")
+        atexit.register(shutil.rmtree, d, True)
+        for f, g in (("small.db", "small.db"), ("small.idx", ".small.idx"), ("small.bps", ".small.bps"), ("small.las", "small.las")):
+            shutil.copy(os.path.join(FIX, f), os.path.join(d, g))
+        _fixdir = d
+    return os.path.join(_fixdir, "small.db"), os.path.join(_fixdir, "small.las")
+
+
+class _Lazy:
+    def __init__(self, i):
+        self.i = i
+
+    def __fspath__(self):
+        return fixture_paths()[self.i]
+
+    def __str__(self):
+        return fixture_paths()[self.i]
+
+    def encode(self):
+        return fixture_paths()[self.i].encode()
+
+
+DB, LAS = _Lazy(0), _Lazy(1)
 
 
 def gold():

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Generates the dazcon fixture and its goldens FROM THE UNMODIFIED REFERENCE, in this container:
-  tests/golden/daz/{small.db,.small.idx,.small.bps,small.las}   a synthetic DAZZ_DB + daligner LAS pair
+  tests/golden/daz/{small.db,small.idx,small.bps,small.las}   a synthetic DAZZ_DB + daligner LAS pair
       (DAZZ_DB simulator | fasta2DB; DBsplit; daligner; LAsort; LAmerge -- SURVEY.md 8(d) cfg 3, built by oracle/Makefile)
   tests/golden/golden_dazcon.json   per flag set: FASTA md5 + (header, md5(seq)) of `dazcon_ref -j 1` (the header-exact
       oracle) and the md5 of the reference DazAlnProvider's dump (oracle/_ref/libdaz_ref.so)
@@ -53,9 +53,14 @@ def main():
         parts = sorted(p for p in os.listdir(tmp) if p.startswith("small.small.") and p.endswith(".las"))
         run([os.path.join(REF, "LAsort")] + parts)
         run([os.path.join(REF, "LAmerge"), "small.las"] + [p[:-4] + ".S.las" for p in parts])
-        for f in ("small.db", ".small.idx", ".small.bps", "small.las"):
-            shutil.copy(os.path.join(tmp, f), os.path.join(OUT, f))
-    db, las = os.path.join(OUT, "small.db"), os.path.join(OUT, "small.las")
+        # the DB's hidden companions are committed under visible names (snapshots of the tree skip dot files); the tests
+        # put them back as .small.idx / .small.bps in a scratch directory (tests/daz_helpers.py: fixture_dir)
+        for f, g in (("small.db", "small.db"), (".small.idx", "small.idx"), (".small.bps", "small.bps"), ("small.las", "small.las")):
+            shutil.copy(os.path.join(tmp, f), os.path.join(OUT, g))
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import daz_helpers
+    db, las = daz_helpers.fixture_paths()
     gold = {"recipe": "simulator 0.03 -c25 -m5000 -s1000 -x2000 -e.15 -r7 | fasta2DB; DBsplit -x500 -s200; daligner; LAsort; LAmerge",
             "runs": [], "dumps": []}
     for r in RUNS:

@@ -47,7 +47,7 @@ def test_provider_dump_matches_reference_goldens():
     md5 equal to the reference provider's dump recorded in golden_dazcon.json."""
     h = dh.host()
     for d in dh.gold()["dumps"]:
-        s = h.dump(dh.DB, dh.LAS, d["min_cov"], d["max_hits"], d["sort_cov"], d["proper"], d["targets"])
+        s = h.dump(str(dh.DB), str(dh.LAS), d["min_cov"], d["max_hits"], d["sort_cov"], d["proper"], d["targets"])
         assert len(s) == d["bytes"] and dh.md5(s) == d["md5"], d
         assert len(dh.parse_dump(s)) == d["n_targets"]
 
@@ -56,17 +56,17 @@ def test_provider_dump_matches_reference_goldens():
 def test_provider_dump_matches_reference_live():
     h, r = dh.host(), dh.ref()
     for kw in (dict(), dict(min_cov=2, max_hits=5, sort_cov=1), dict(proper=1, min_cov=1), dict(targets=(1, 2, 77, 137, 138), min_cov=3)):
-        a, b = h.dump(dh.DB, dh.LAS, **kw), r.dump(dh.DB, dh.LAS, **kw)
+        a, b = h.dump(str(dh.DB), str(dh.LAS), **kw), r.dump(str(dh.DB), str(dh.LAS), **kw)
         assert a == b, kw
-    t = dh.parse_dump(h.dump(dh.DB, dh.LAS))
+    t = dh.parse_dump(h.dump(str(dh.DB), str(dh.LAS)))
     assert len(t) > 100 and all(len(seq) == tlen for _, tlen, seq, _ in t)
     assert all(len(q) == len(tt) for _, _, _, alns in t for _, _, q, tt in alns)
 
 
 def test_missing_inputs_fail_loudly(tmp_path):
-    r = subprocess.run([dh.DAZCON, "-a", dh.LAS], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    r = subprocess.run([dh.DAZCON, "-a", str(dh.LAS)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     assert r.returncode == 1 and "seq-file" in r.stderr
-    r = subprocess.run([dh.DAZCON, "-s", dh.DB], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    r = subprocess.run([dh.DAZCON, "-s", str(dh.DB)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     assert r.returncode == 1 and "align-file" in r.stderr
     h = dh.host()
-    assert h.dump(dh.DB, str(tmp_path / "nope.las")).startswith(b"ERROR Open failed")
+    assert h.dump(str(dh.DB), str(tmp_path / "nope.las")).startswith(b"ERROR Open failed")

@@ -22,7 +22,7 @@ def run(exe, args, timeout=600, env=None):
 
 def test_dazcon_fixture_goldens():
     for g in dh.gold()["runs"]:
-        out = run(dh.DAZCON, ["-j", "4", "-s", dh.DB, "-a", dh.LAS] + g["flags"])
+        out = run(dh.DAZCON, ["-j", "4", "-s", str(dh.DB), "-a", str(dh.LAS)] + g["flags"])
         lines = out.split(b"\n")
         recs = [[lines[i].decode(), dh.md5(lines[i + 1])] for i in range(0, len(lines) - 1, 2)]
         assert recs == g["records"], g["name"]
@@ -32,13 +32,13 @@ def test_dazcon_fixture_goldens():
 @pytest.mark.skipif(not os.path.exists(dh.DAZCON_REF), reason="oracle/_ref/dazcon_ref did not travel")
 def test_dazcon_fixture_live_against_reference_binary():
     for flags in (["-c", "8", "-t", "20"], ["-x", "-m", "12", "-l", "1000"]):
-        ref = run(dh.DAZCON_REF, ["-j", "1", "-s", dh.DB, "-a", dh.LAS] + flags)
+        ref = run(dh.DAZCON_REF, ["-j", "1", "-s", str(dh.DB), "-a", str(dh.LAS)] + flags)
         for extra in ([], ["--batch-targets", "7", "-j", "3"]):
-            assert run(dh.DAZCON, ["-s", dh.DB, "-a", dh.LAS] + flags + extra) == ref, (flags, extra)
+            assert run(dh.DAZCON, ["-s", str(dh.DB), "-a", str(dh.LAS)] + flags + extra) == ref, (flags, extra)
     # several handles (shared device on a one-GPU box): same bytes, same well counter
     env = dict(os.environ, DGC_SHARE_GPUS="1")
-    one = run(dh.DAZCON, ["-s", dh.DB, "-a", dh.LAS, "--batch-targets", "9"])
-    assert run(dh.DAZCON, ["-s", dh.DB, "-a", dh.LAS, "--batch-targets", "9", "--gpus", "3"], env=env) == one
+    one = run(dh.DAZCON, ["-s", str(dh.DB), "-a", str(dh.LAS), "--batch-targets", "9"])
+    assert run(dh.DAZCON, ["-s", str(dh.DB), "-a", str(dh.LAS), "--batch-targets", "9", "--gpus", "3"], env=env) == one
 
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(REFDIR, "daligner")), reason="dazzler tools did not travel")
