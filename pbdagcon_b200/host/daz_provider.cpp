@@ -22,6 +22,7 @@
 #include <atomic>
 #include <chrono>
 #include <cstring>
+#include <mutex>
 #include <numeric>
 #include <thread>
 
@@ -178,9 +179,15 @@ struct DazDb::Impl {
     HITS_DB db;
     bool open = false;
 };
+// The dazzler library builds file names in static buffers (DAZZ_DB/DB.c: Catenate, PathTo): everything that opens a
+// file -- Open_DB, and the first Load_Subread of a handle, which opens the .bps -- runs under this lock.  Reads
+// after that are per handle and need no lock.
+static std::mutex g_daz_open_mu;
+
 DazDb::DazDb(const std::string& path) : impl_(new Impl) {
     std::vector<char> p(path.begin(), path.end());
     p.push_back('\0');                       // Open_DB wants a mutable string
+    std::lock_guard<std::mutex> lk(g_daz_open_mu);
     if (Open_DB(p.data(), &impl_->db) < 0) throw PacBio::DagCon::IOException("Failed to open DB");
     impl_->open = true;
     Trim_DB(&impl_->db);
@@ -205,6 +212,10 @@ struct Realizer::Impl {
         bbuf = New_Read_Buffer(h);
         tbuf = New_Read_Buffer(h);
         if (!work || !abuf || !bbuf || !tbuf) throw PacBio::DagCon::IOException("Failed to allocate dazzler work buffers");
+        if (h->nreads > 0 && h->reads[0].rlen > 0) {   // opens the .bps now, under the lock (see g_daz_open_mu)
+            std::lock_guard<std::mutex> lk(g_daz_open_mu);
+            if (!Load_Subread(h, 0, 0, 1, tbuf, 0)) throw PacBio::DagCon::IOException("Failed to open the DB's base file");
+        }
     }
     ~Impl() {
         if (abuf) free(abuf - 1);
