@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DGC_ABI_VERSION 1
+#define DGC_ABI_VERSION 2
 #define DGC_MAX_INFLIGHT 4 /* batches that may be submitted and not yet collected */
 
 /* error codes (function return values) */
@@ -32,6 +32,7 @@ extern "C" {
 #define DGC_E_NOMEM (-3)     /* a single target does not fit the scratch budget */
 #define DGC_E_STATE (-4)     /* collect without submit, etc. */
 #define DGC_E_NODEVICE (-5)  /* no usable CUDA device (there is no CPU fallback) */
+#define DGC_E_DAZ (-6)       /* dgc_submit_daz: an overlap the device realignment cannot take (trace values out of range) */
 
 /* per-target status (dgc_results.tgt_status) */
 #define DGC_T_OK 0
@@ -104,6 +105,8 @@ typedef struct dgc_timings {
     uint64_t arena_bytes;    /* graph arena bytes used (sum over chunks) */
     uint64_t norm_cols;      /* normalised+trimmed columns fed to the graph */
     uint64_t nodes, edges;   /* pre-merge graph size, summed over targets */
+    float ms_realign;        /* dgc_submit_daz: trace-point realignment + string emission */
+    uint32_t reserved1;
 } dgc_timings;
 
 typedef struct dgc_handle dgc_handle;
@@ -130,6 +133,47 @@ int dgc_host_free(void* p);
  * Replaces AlnBuf::push / CnsBuf::pop (main.cpp:87,120,144,168). */
 int dgc_submit(dgc_handle* h, const dgc_batch* batch);
 int dgc_collect(dgc_handle* h, dgc_results* out);
+
+/* ---- dazcon: overlaps in, consensus out (the trace-point realignment runs on the device) -------------------------
+ * Replaces the per-overlap work of the reference's Reader thread, Target::getAlignments
+ * (src/cpp/DazAlnProvider.cpp:304-369: Load_Subread, Complement_Seq, Compute_Trace_PTS(GREEDIEST) =
+ * DALIGNER/align.c:4799-4896 + iter_np :4132-4459, decodeAlignment :383-417) and the target-sequence load of
+ * DazAlnProvider::nextTarget(targSeq, dest) (:119-131).  Hit selection (TargetHit scoring, sortHits, the max-hit cap
+ * and the provider's min-coverage filter) stays with the caller: a batch lists, per target, the overlaps that
+ * getAlignments would turn into alignments, in that order. */
+typedef struct dgc_daz_db {      /* the trimmed DAZZ_DB (Open_DB + Trim_DB): stays resident on the device */
+    uint32_t n_reads;
+    const uint64_t* read_boff;   /* [n_reads] HITS_READ.boff: byte offset of the read in `bases` */
+    const uint32_t* read_len;    /* [n_reads] HITS_READ.rlen */
+    const uint8_t* bases;        /* the .bps file: 2 bits per base, 4 bases per byte, first base in the top bits */
+    uint64_t bases_bytes;
+} dgc_daz_db;
+
+typedef struct dgc_daz_batch {
+    uint32_t n_targets;
+    uint32_t n_ovls;
+    uint32_t tspace;                /* trace spacing of the LAS file; must be <= 125 (byte-wide trace values) */
+    const uint32_t* tgt_aread;      /* [n_targets] the A read (0-based DB index); FASTA id = aread + 1 */
+    const uint32_t* tgt_ovl_begin;  /* [n_targets+1] CSR into the overlap arrays */
+    const uint32_t* ovl_bread;      /* [n_ovls] */
+    const uint32_t* ovl_comp;       /* [n_ovls] COMP(flags): B is reverse-complemented */
+    const int32_t* ovl_abpos;       /* [n_ovls] Path.abpos / aepos / bbpos / bepos */
+    const int32_t* ovl_aepos;
+    const int32_t* ovl_bbpos;
+    const int32_t* ovl_bepos;
+    const uint64_t* ovl_trace_off;  /* [n_ovls] first trace value of the overlap in `trace` */
+    const uint32_t* ovl_tlen;       /* [n_ovls] Path.tlen: number of trace values (pairs: diffs, B advance); even, >= 2 */
+    const uint8_t* trace;
+    uint64_t trace_bytes;
+} dgc_daz_batch;
+
+int dgc_daz_set_db(dgc_handle* h, const dgc_daz_db* db);
+/* Same pipeline discipline as dgc_submit (results through dgc_collect, in submit order, dgc_results unchanged). */
+int dgc_submit_daz(dgc_handle* h, const dgc_daz_batch* batch);
+/* Test hook: the gapped strings the device writes for every overlap of a batch (what decodeAlignment produces):
+ * q/t of overlap k at out_off[k] .. +out_len[k] in out_q / out_t (capacity out_cap bytes each). */
+int dgc_debug_daz_strings(dgc_handle* h, const dgc_daz_batch* batch, uint8_t* out_q, uint8_t* out_t, uint64_t out_cap,
+                          uint64_t* out_off, uint32_t* out_len);
 
 /* Synchronous convenience: submit + collect. */
 int dgc_consensus(dgc_handle* h, const dgc_batch* batch, dgc_results* out);

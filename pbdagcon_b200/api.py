@@ -19,7 +19,8 @@ MAX_INFLIGHT = 4
 
 EXPORTS = ["dgc_abi_version", "dgc_device_count", "dgc_create", "dgc_destroy", "dgc_last_error", "dgc_host_alloc",
            "dgc_host_free", "dgc_submit", "dgc_collect", "dgc_consensus", "dgc_upload", "dgc_run", "dgc_dbatch_free",
-           "dgc_get_timings", "dgc_debug_normalize", "dgc_debug_graph", "dgc_debug_free"]
+           "dgc_get_timings", "dgc_debug_normalize", "dgc_debug_graph", "dgc_debug_free",
+           "dgc_daz_set_db", "dgc_submit_daz", "dgc_debug_daz_strings"]
 
 
 class DagconError(RuntimeError):
@@ -50,7 +51,7 @@ class Timings(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("ms_h2d", "ms_normalize", "ms_count", "ms_build", "ms_merge", "ms_bestpath",
                                          "ms_compact", "ms_d2h", "ms_total", "ms_span")] + \
                [("launches", C.c_uint32), ("chunks", C.c_uint32), ("arena_bytes", C.c_uint64), ("norm_cols", C.c_uint64),
-                ("nodes", C.c_uint64), ("edges", C.c_uint64)]
+                ("nodes", C.c_uint64), ("edges", C.c_uint64), ("ms_realign", C.c_float), ("reserved1", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -8,6 +8,7 @@
 // overlaps the kernels of batch k.  There is no CPU implementation of any stage in here.
 #include "../../include/dagcon_b200.h"
 #include "dagcon_kernels.cuh"
+#include "daz_realign.cuh"
 
 #include <algorithm>
 #include <condition_variable>
@@ -99,7 +100,7 @@ struct EventPool {
     void destroy() { for (auto e : ev) cudaEventDestroy(e); ev.clear(); }
 };
 
-enum Phase { PH_H2D, PH_NORM, PH_COUNT, PH_BUILD, PH_MERGE, PH_PATH, PH_COMPACT, PH_D2H, PH_N };
+enum Phase { PH_H2D, PH_NORM, PH_COUNT, PH_BUILD, PH_MERGE, PH_PATH, PH_COMPACT, PH_D2H, PH_DAZ, PH_N };
 
 struct Slot {
     dgc_handle* h = nullptr;
@@ -134,6 +135,12 @@ struct Slot {
     std::condition_variable cv;
     enum State { IDLE, QUEUED, RUNNING, DONE, STOP } state = IDLE;
     dgc_batch pending{};  // copied at submit: only the arrays it points to must outlive the call
+    dgc_daz_batch pending_daz{};
+    bool is_daz = false;
+    // dazcon realignment (daz_realign.cuh): per-overlap inputs, per-segment work arrays, edit scripts, wave slabs
+    DevBuf z_aread, z_bread, z_comp, z_abpos, z_aepos, z_bbpos, z_bepos, z_troff, z_tlen, z_segb, z_eoff, z_trace, z_tgt_aread;
+    DevBuf z_seg_bb, z_seg_eoff, z_seg_cnt, z_seg_neg, z_seg_ppos, z_seg_pneg, z_entries, z_vf, z_hf, z_err;
+    HostBuf zh_plan;
     uint64_t seq = 0;     // submit sequence number of `pending`
     uint64_t hint[5] = {0, 0, 0, 0, 0};  // arena needs (units, positions, cons, frags, scratch) of the last staged batch that fit one chunk
     int rc = 0;
@@ -165,6 +172,10 @@ struct dgc_handle {
     std::mutex q_mu;
     std::deque<int> inflight;
     bool busy[NSLOT] = {};
+    // dazcon: the read database, resident (dgc_daz_set_db)
+    DevBuf daz_bases, daz_boff, daz_rlen;
+    std::vector<uint32_t> daz_h_rlen;
+    uint32_t daz_n_reads = 0;
 };
 
 namespace {
@@ -958,6 +969,7 @@ void finish_timings(Slot& s) {
     }
     s.tm.ms_h2d = acc[PH_H2D]; s.tm.ms_normalize = acc[PH_NORM]; s.tm.ms_count = acc[PH_COUNT]; s.tm.ms_build = acc[PH_BUILD];
     s.tm.ms_merge = acc[PH_MERGE]; s.tm.ms_bestpath = acc[PH_PATH]; s.tm.ms_compact = acc[PH_COMPACT]; s.tm.ms_d2h = acc[PH_D2H];
+    s.tm.ms_realign = acc[PH_DAZ];
     s.tm.ms_total = 0;
     for (int i = 0; i < PH_N; i++) s.tm.ms_total += acc[i];
     s.tm.ms_span = 0;
@@ -971,7 +983,10 @@ void begin_run(Slot& s) {
     s.err.clear();
 }
 
+int slot_process_daz(Slot& s, const dgc_daz_batch* b);
+
 int slot_process(Slot& s, const dgc_batch* b) {
+    if (s.is_daz) return slot_process_daz(s, &s.pending_daz);
     begin_run(s);
     dgc_handle* h = s.h;
     {
@@ -990,6 +1005,195 @@ int slot_process(Slot& s, const dgc_batch* b) {
         if (rc == DGC_OK) rc = run_pipeline(s, s.db, 2, 0xFFFFFFFFu);
     }
     cudaStreamSynchronize(s.copy_stream);
+    cudaStreamSynchronize(s.stream);
+    finish_timings(s);
+    return rc;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// dgc_submit_daz: the overlaps' gapped strings are built on the device (daz_realign.cuh) inside the slot's batch arena,
+// then the batch runs through the same kernels as any other.  All sizes the planner needs are bounds that follow
+// from the trace points: an overlap has at most (aepos - abpos + 1) + sum(diffs) columns.
+int validate_daz(const dgc_handle* h, const dgc_daz_batch* b, std::string& err) {
+    if (!b) { err = "null batch"; return DGC_E_INVALID; }
+    if (!h->daz_n_reads) { err = "dgc_daz_set_db has not been called"; return DGC_E_STATE; }
+    if (b->tspace == 0 || b->tspace > 125) { err = "trace spacing above 125 (two-byte trace values): realign on the host"; return DGC_E_DAZ; }
+    if (b->n_targets && (!b->tgt_aread || !b->tgt_ovl_begin)) { err = "null target arrays"; return DGC_E_INVALID; }
+    if (b->n_ovls && (!b->ovl_bread || !b->ovl_comp || !b->ovl_abpos || !b->ovl_aepos || !b->ovl_bbpos || !b->ovl_bepos ||
+                      !b->ovl_trace_off || !b->ovl_tlen || !b->trace)) { err = "null overlap arrays"; return DGC_E_INVALID; }
+    if (b->n_targets && (b->tgt_ovl_begin[0] != 0 || b->tgt_ovl_begin[b->n_targets] != b->n_ovls)) { err = "tgt_ovl_begin is not a CSR over n_ovls"; return DGC_E_INVALID; }
+    for (uint32_t t = 0; t < b->n_targets; t++) {
+        if (b->tgt_ovl_begin[t + 1] < b->tgt_ovl_begin[t]) { err = "tgt_ovl_begin not monotone"; return DGC_E_INVALID; }
+        if (b->tgt_aread[t] >= h->daz_n_reads) { err = "A read outside the DB"; return DGC_E_INVALID; }
+        const int alen = (int)h->daz_h_rlen[b->tgt_aread[t]];
+        for (uint32_t k = b->tgt_ovl_begin[t]; k < b->tgt_ovl_begin[t + 1]; k++) {
+            if (b->ovl_bread[k] >= h->daz_n_reads) { err = "B read outside the DB"; return DGC_E_INVALID; }
+            const int blen = (int)h->daz_h_rlen[b->ovl_bread[k]];
+            const int ab = b->ovl_abpos[k], ae = b->ovl_aepos[k], bb = b->ovl_bbpos[k], be = b->ovl_bepos[k];
+            if (ab < 0 || ae < ab || ae > alen || bb < 0 || be < bb || be > blen) { err = "overlap coordinates outside its reads"; return DGC_E_INVALID; }
+            const uint32_t tl = b->ovl_tlen[k];
+            if (tl < 2 || (tl & 1)) { err = "overlap without trace points"; return DGC_E_DAZ; }
+            if (b->ovl_trace_off[k] > b->trace_bytes || tl > b->trace_bytes - b->ovl_trace_off[k]) { err = "trace outside its array"; return DGC_E_INVALID; }
+            // the segments the trace points imply must tile [abpos, aepos) x [bbpos, bepos)
+            const uint32_t nseg = tl / 2, want = (uint32_t)(ae / (int)b->tspace - ab / (int)b->tspace) + ((ae % (int)b->tspace) ? 1u : 0u);
+            if (nseg != (want ? want : 1u)) { err = "trace length does not match the overlap's A interval"; return DGC_E_DAZ; }
+            const uint8_t* p = b->trace + b->ovl_trace_off[k];
+            int64_t sb = bb;
+            for (uint32_t i = 0; i + 1 < nseg; i++) sb += p[2 * i + 1];
+            if (sb > be || be - sb > DZ_MAX_N) { err = "trace points do not fit the overlap's B interval"; return DGC_E_DAZ; }
+        }
+    }
+    return DGC_OK;
+}
+
+int build_daz_batch(Slot& s, const dgc_daz_batch* b, bool strings_only) {
+    dgc_handle* h = s.h;
+    dgc_dbatch& db = s.db;
+    cudaStream_t st = s.stream;
+    const size_t T = b->n_targets, O = b->n_ovls;
+    // ---- host planning: offsets of everything from the trace-point bounds
+    // plan layout: u32 tlen[T+1] | u32 start[O+1] | u32 segb[O+1] | u64 bb_off[T+1] | u64 q_off[O+1] | u64 t_off[O+1] | u64 norm_off[O+1] | u64 entry_off[O+1]
+    CU(s.zh_plan.ensure(4 * (T + 1) + 8 * (O + 1) + 8 * (T + 1) + 32 * (O + 1) + 64));
+    uint32_t* p_tlen = s.zh_plan.as<uint32_t>();
+    uint32_t* p_start = p_tlen + (T + 1);
+    uint32_t* p_segb = p_start + (O + 1);
+    uint64_t* p_bb = (uint64_t*)(p_segb + (O + 1) + ((T + 1 + 2 * (O + 1)) & 1));
+    uint64_t* p_q = p_bb + (T + 1);
+    uint64_t* p_t = p_q + (O + 1);
+    uint64_t* p_norm = p_t + (O + 1);
+    uint64_t* p_ent = p_norm + (O + 1);
+    uint64_t arena = 0, norm = 0, ent = 0, raw = 0;
+    uint32_t nseg_tot = 0, dmax = 0, nmax = 0;
+    for (size_t t = 0; t < T; t++) {
+        const uint32_t L = h->daz_h_rlen[b->tgt_aread[t]];
+        p_tlen[t] = L;
+        p_bb[t] = arena;
+        arena += ((uint64_t)L + 15) & ~15ull;
+        for (uint32_t k = b->tgt_ovl_begin[t]; k < b->tgt_ovl_begin[t + 1]; k++) {
+            const uint8_t* p = b->trace + b->ovl_trace_off[k];
+            const uint32_t nseg = b->ovl_tlen[k] / 2;
+            uint64_t sumd = 0, sb = (uint64_t)b->ovl_bbpos[k];
+            for (uint32_t i = 0; i < nseg; i++) {
+                sumd += p[2 * i];
+                dmax = std::max<uint32_t>(dmax, p[2 * i]);
+                if (i + 1 < nseg) { nmax = std::max<uint32_t>(nmax, p[2 * i + 1]); sb += p[2 * i + 1]; }
+            }
+            nmax = std::max<uint32_t>(nmax, (uint32_t)((uint64_t)b->ovl_bepos[k] - sb));
+            const uint64_t cols = (uint64_t)(b->ovl_aepos[k] - b->ovl_abpos[k] + 1) + sumd;
+            p_start[k] = (uint32_t)(b->ovl_abpos[k] + 1);            // dagcon::Alignment::start (:356)
+            p_segb[k] = nseg_tot;
+            p_q[k] = arena; arena += (cols + 15) & ~15ull;
+            p_t[k] = arena; arena += (cols + 15) & ~15ull;
+            p_norm[k] = norm; norm += (2 * cols + 7) & ~7ull;
+            p_ent[k] = ent; ent += sumd;
+            raw += cols;
+            nseg_tot += nseg;
+        }
+    }
+    p_segb[O] = nseg_tot;
+    if (arena > (1ull << 40) || nseg_tot > 0x7FFFFFF0u) { s.err = "dazcon batch too large"; return DGC_E_NOMEM; }
+    db.T = (uint32_t)T; db.A = (uint32_t)O; db.has_bb = true; db.arena_bytes = arena; db.norm_cols = norm; db.raw_cols = raw;
+    db.h_tlen.assign(p_tlen, p_tlen + T);
+    db.h_aln_begin.assign(b->tgt_ovl_begin, b->tgt_ovl_begin + T + 1);
+    if (T == 0) return DGC_OK;
+    CU(db.tgt_tlen.ensure(4 * (T + 1))); CU(db.tgt_aln_begin.ensure(4 * (T + 1))); CU(db.tgt_bb_off.ensure(8 * (T + 1)));
+    CU(db.aln_start.ensure(4 * (O + 1))); CU(db.aln_len.ensure(4 * (O + 1)));
+    CU(db.aln_q_off.ensure(8 * (O + 1))); CU(db.aln_t_off.ensure(8 * (O + 1))); CU(db.aln_norm_off.ensure(8 * (O + 1)));
+    CU(db.arena.ensure(arena + 64));
+    for (DevBuf* d : {&s.z_bread, &s.z_comp, &s.z_abpos, &s.z_aepos, &s.z_bbpos, &s.z_bepos, &s.z_tlen, &s.z_segb, &s.z_aread}) CU(d->ensure(4 * (O + 1)));
+    CU(s.z_troff.ensure(8 * (O + 1))); CU(s.z_eoff.ensure(8 * (O + 1))); CU(s.z_tgt_aread.ensure(4 * (T + 1)));
+    CU(s.z_trace.ensure(b->trace_bytes + 16));
+    CU(s.z_seg_bb.ensure(4ull * nseg_tot + 16)); CU(s.z_seg_eoff.ensure(4ull * nseg_tot + 16));
+    for (DevBuf* d : {&s.z_seg_cnt, &s.z_seg_neg, &s.z_seg_ppos, &s.z_seg_pneg}) CU(d->ensure(2ull * nseg_tot + 16));
+    CU(s.z_entries.ensure(4 * ent + 16));
+    CU(s.z_err.ensure(16));
+    // wave slabs: rows x width cells per thread, as many threads as the budget allows
+    const uint32_t rows = dmax + 3;
+    const uint32_t koff = nmax + dmax / 2 + 4;
+    const uint32_t width = koff + std::max<uint32_t>(b->tspace, DZ_MAX_M) + dmax / 2 + 6;
+    const uint64_t slab_cells = (uint64_t)rows * width;
+    uint64_t n_slabs = std::min<uint64_t>(nseg_tot, (uint64_t)h->sm_count * 512);
+    n_slabs = std::max<uint64_t>(1, std::min<uint64_t>(n_slabs, (3ull << 30) / (3 * slab_cells)));
+    CU(s.z_vf.ensure(2 * slab_cells * n_slabs + 64)); CU(s.z_hf.ensure(slab_cells * n_slabs + 64));
+    // per-overlap A read (the kernels index overlaps, not targets)
+    std::vector<uint32_t> aread(O);
+    for (size_t t = 0; t < T; t++)
+        for (uint32_t k = b->tgt_ovl_begin[t]; k < b->tgt_ovl_begin[t + 1]; k++) aread[k] = b->tgt_aread[t];
+    span_begin(s, PH_H2D);
+    CU(cudaMemcpyAsync(db.tgt_tlen.p, p_tlen, 4 * T, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(db.tgt_aln_begin.p, b->tgt_ovl_begin, 4 * (T + 1), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(db.tgt_bb_off.p, p_bb, 8 * T, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.z_tgt_aread.p, b->tgt_aread, 4 * T, cudaMemcpyHostToDevice, st));
+    if (O) {
+        CU(cudaMemcpyAsync(db.aln_start.p, p_start, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db.aln_q_off.p, p_q, 8 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db.aln_t_off.p, p_t, 8 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db.aln_norm_off.p, p_norm, 8 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_aread.p, aread.data(), 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_bread.p, b->ovl_bread, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_comp.p, b->ovl_comp, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_abpos.p, b->ovl_abpos, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_aepos.p, b->ovl_aepos, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_bbpos.p, b->ovl_bbpos, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_bepos.p, b->ovl_bepos, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_tlen.p, b->ovl_tlen, 4 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_troff.p, b->ovl_trace_off, 8 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_segb.p, p_segb, 4 * (O + 1), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_eoff.p, p_ent, 8 * O, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.z_trace.p, b->trace, b->trace_bytes, cudaMemcpyHostToDevice, st));
+    }
+    CU(cudaMemsetAsync(s.z_err.p, 0, 16, st));
+    span_end(s);
+    CU(cudaStreamSynchronize(st));   // `aread` and the caller's arrays may go; the link is free for the next batch
+    release_h2d_turn_now(h, s.seq + 1);
+    if (O == 0 && !strings_only) return DGC_OK;
+    DazArgs a;
+    a.db.bases = h->daz_bases.as<u8>(); a.db.boff = h->daz_boff.as<u64>(); a.db.rlen = h->daz_rlen.as<u32>();
+    a.n_ovl = (u32)O; a.n_seg = nseg_tot; a.tspace = b->tspace;
+    a.ovl_aread = s.z_aread.as<u32>(); a.ovl_bread = s.z_bread.as<u32>(); a.ovl_comp = s.z_comp.as<u32>();
+    a.ovl_abpos = s.z_abpos.as<int>(); a.ovl_aepos = s.z_aepos.as<int>(); a.ovl_bbpos = s.z_bbpos.as<int>(); a.ovl_bepos = s.z_bepos.as<int>();
+    a.ovl_trace_off = s.z_troff.as<u64>(); a.ovl_tlen = s.z_tlen.as<u32>(); a.ovl_seg_begin = s.z_segb.as<u32>();
+    a.ovl_entry_off = s.z_eoff.as<u64>(); a.trace = s.z_trace.as<u8>();
+    a.seg_bb = s.z_seg_bb.as<int>(); a.seg_eoff = s.z_seg_eoff.as<u32>(); a.seg_cnt = s.z_seg_cnt.as<u16>(); a.seg_neg = s.z_seg_neg.as<u16>();
+    a.seg_ppos = s.z_seg_ppos.as<u16>(); a.seg_pneg = s.z_seg_pneg.as<u16>(); a.entries = s.z_entries.as<int>();
+    a.vf = s.z_vf.as<short>(); a.hf = s.z_hf.as<signed char>(); a.rows = rows; a.width = width; a.koff = koff; a.n_slabs = (u32)n_slabs;
+    a.arena = db.arena.as<u8>(); a.aln_q_off = db.aln_q_off.as<u64>(); a.aln_t_off = db.aln_t_off.as<u64>(); a.aln_len = db.aln_len.as<u32>();
+    a.error = s.z_err.as<u32>();
+    span_begin(s, PH_DAZ);
+    if (O) {
+        k_daz_prep<<<(unsigned)((O + 127) / 128), 128, 0, st>>>(a);
+        k_daz_iter<<<(unsigned)((n_slabs + 127) / 128), 128, 0, st>>>(a);
+        k_daz_scan<<<(unsigned)((O + 127) / 128), 128, 0, st>>>(a);
+        k_daz_emit<<<(nseg_tot + 127) / 128, 128, 0, st>>>(a);
+        s.tm.launches += 4;
+    }
+    k_daz_backbone<<<(unsigned)T, 256, 0, st>>>(a.db, (u32)T, s.z_tgt_aread.as<u32>(), db.tgt_bb_off.as<u64>(), db.arena.as<u8>());
+    s.tm.launches++;
+    CU(cudaGetLastError());
+    span_end(s);
+    uint32_t zerr = 0;
+    CU(cudaMemcpyAsync(&zerr, s.z_err.p, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (zerr) { s.err = "device realignment failed on a segment (code " + std::to_string(zerr) + "): the trace points do not bound its edits"; return DGC_E_DAZ; }
+    return DGC_OK;
+}
+
+int slot_process_daz(Slot& s, const dgc_daz_batch* b) {
+    begin_run(s);
+    dgc_handle* h = s.h;
+    {
+        std::unique_lock<std::mutex> lk(h->h2d_mu);
+        h->h2d_cv.wait(lk, [&] { return h->h2d_turn == s.seq; });
+    }
+    bool released = false;
+    int rc = build_daz_batch(s, b, false);
+    {   // build_daz_batch hands the link on once its arrays have landed; on an early error do it here
+        std::lock_guard<std::mutex> lk(h->h2d_mu);
+        released = h->h2d_turn > s.seq;
+    }
+    if (!released) release_h2d_turn_now(h, s.seq + 1);
+    if (rc == DGC_OK) rc = run_pipeline(s, s.db, 2, 0xFFFFFFFFu);
     cudaStreamSynchronize(s.stream);
     finish_timings(s);
     return rc;
@@ -1097,8 +1301,11 @@ int dgc_destroy(dgc_handle* h) {
         for (DevBuf* b : {&s.o_off, &s.o_len, &s.o_start, &s.o_flags, &s.o_nI, &s.o_nE, &s.o_tkept, &s.norm, &s.t_status, &s.t_V,
                           &s.t_E, &s.t_cols, &s.t_ne, &s.t_nv, &s.t_cons_len, &s.t_nfrag, &s.t_cons_coff, &s.t_frag_coff, &s.totals,
                           &s.rec_off, &s.pos_off, &s.pool_cap, &s.t_pool_top, &s.cons_off, &s.frag_off, &s.frag_cap, &s.gs_off, &s.gs_cap,
-                          &s.rec, &s.cons, &s.frags, &s.gscratch, &s.gacc, &s.out_cons, &s.out_frags})
+                          &s.rec, &s.cons, &s.frags, &s.gscratch, &s.gacc, &s.out_cons, &s.out_frags, &s.z_aread, &s.z_bread, &s.z_comp,
+                          &s.z_abpos, &s.z_aepos, &s.z_bbpos, &s.z_bepos, &s.z_troff, &s.z_tlen, &s.z_segb, &s.z_eoff, &s.z_trace, &s.z_tgt_aread,
+                          &s.z_seg_bb, &s.z_seg_eoff, &s.z_seg_cnt, &s.z_seg_neg, &s.z_seg_ppos, &s.z_seg_pneg, &s.z_entries, &s.z_vf, &s.z_hf, &s.z_err})
             b->release();
+        s.zh_plan.release();
         for (HostBuf* b : {&s.h_norm_off, &s.hp_plan_in, &s.hp_plan_out, &s.r_status, &s.r_cons_coff, &s.r_frag_coff, &s.r_totals,
                            &s.r_cons, &s.r_frags, &s.r_nfrag})
             b->release();
@@ -1106,6 +1313,7 @@ int dgc_destroy(dgc_handle* h) {
         cudaStreamDestroy(s.stream);
         if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
     }
+    h->daz_bases.release(); h->daz_boff.release(); h->daz_rlen.release();
     delete h;
     return DGC_OK;
 }
@@ -1139,6 +1347,7 @@ int dgc_submit(dgc_handle* h, const dgc_batch* batch) {
         std::unique_lock<std::mutex> lk(s.mu);
         s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
         s.pending = *batch;
+        s.is_daz = false;
         s.seq = h->submitted;
         s.state = Slot::QUEUED;
         s.cv.notify_all();
@@ -1172,6 +1381,89 @@ int dgc_collect(dgc_handle* h, dgc_results* out) {
     }
     if (rc) { h->err = s.err; return rc; }
     *out = s.results;
+    return DGC_OK;
+}
+
+
+int dgc_daz_set_db(dgc_handle* h, const dgc_daz_db* d) {
+    if (!h || !d || !d->n_reads || !d->read_boff || !d->read_len || !d->bases) { if (h) h->err = "bad dgc_daz_db"; return DGC_E_INVALID; }
+    if (h->submitted != h->collected) { h->err = "dgc_daz_set_db while batches are in flight"; return DGC_E_STATE; }
+    for (uint32_t i = 0; i < d->n_reads; i++)
+        if (d->read_boff[i] > d->bases_bytes || ((uint64_t)d->read_len[i] + 3) / 4 > d->bases_bytes - d->read_boff[i]) { h->err = "read outside the base array"; return DGC_E_INVALID; }
+    cudaSetDevice(h->device);
+    cudaError_t e;
+    if ((e = h->daz_bases.ensure(d->bases_bytes + 16)) != cudaSuccess || (e = h->daz_boff.ensure(8ull * d->n_reads)) != cudaSuccess ||
+        (e = h->daz_rlen.ensure(4ull * d->n_reads)) != cudaSuccess ||
+        (e = cudaMemcpy(h->daz_bases.p, d->bases, d->bases_bytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(h->daz_boff.p, d->read_boff, 8ull * d->n_reads, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(h->daz_rlen.p, d->read_len, 4ull * d->n_reads, cudaMemcpyHostToDevice)) != cudaSuccess) {
+        h->err = cudaGetErrorString(e);
+        return DGC_E_CUDA;
+    }
+    h->daz_h_rlen.assign(d->read_len, d->read_len + d->n_reads);
+    h->daz_n_reads = d->n_reads;
+    return DGC_OK;
+}
+
+int dgc_submit_daz(dgc_handle* h, const dgc_daz_batch* batch) {
+    if (!h) return DGC_E_INVALID;
+    int rc = validate_daz(h, batch, h->err);
+    if (rc) return rc;
+    int si = -1;
+    {
+        std::lock_guard<std::mutex> lk(h->q_mu);
+        if (h->inflight.size() >= (size_t)DGC_MAX_INFLIGHT) { h->err = "too many batches in flight: collect first"; return DGC_E_STATE; }
+        for (int i = 0; i < NSLOT && si < 0; i++)
+            if (!h->busy[i]) si = i;
+        h->busy[si] = true;
+        h->inflight.push_back(si);
+    }
+    Slot& s = h->slots[si];
+    {
+        std::unique_lock<std::mutex> lk(s.mu);
+        s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
+        s.pending_daz = *batch;
+        s.is_daz = true;
+        s.seq = h->submitted;
+        s.state = Slot::QUEUED;
+        s.cv.notify_all();
+    }
+    h->submitted++;
+    return DGC_OK;
+}
+
+int dgc_debug_daz_strings(dgc_handle* h, const dgc_daz_batch* batch, uint8_t* out_q, uint8_t* out_t, uint64_t out_cap,
+                          uint64_t* out_off, uint32_t* out_len) {
+    if (!h || !batch || !out_off || !out_len) return DGC_E_INVALID;
+    if (h->submitted != h->collected) { h->err = "debug call while batches are in flight"; return DGC_E_STATE; }
+    int rc = validate_daz(h, batch, h->err);
+    if (rc) return rc;
+    cudaSetDevice(h->device);
+    Slot& s = h->slots[0];
+    begin_run(s);
+    s.seq = h->h2d_turn;                 // build_daz_batch hands the H2D turn on: keep the counter where it was afterwards
+    const uint64_t turn = h->h2d_turn;
+    rc = build_daz_batch(s, batch, true);
+    release_h2d_turn_now(h, turn);
+    if (rc) { h->err = s.err; return rc; }
+    const size_t O = batch->n_ovls;
+    std::vector<uint64_t> qo(O), to(O);
+    std::vector<uint32_t> ln(O);
+    cudaError_t e = cudaSuccess;
+    if (O) {
+        e = cudaMemcpy(qo.data(), s.db.aln_q_off.p, 8 * O, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(to.data(), s.db.aln_t_off.p, 8 * O, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(ln.data(), s.db.aln_len.p, 4 * O, cudaMemcpyDeviceToHost);
+    }
+    uint64_t pos = 0;
+    for (size_t k = 0; k < O && e == cudaSuccess; k++) {
+        if (pos + ln[k] > out_cap) { h->err = "output buffers too small"; return DGC_E_INVALID; }
+        out_off[k] = pos; out_len[k] = ln[k];
+        e = cudaMemcpy(out_q + pos, (const u8*)s.db.arena.p + qo[k], ln[k], cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(out_t + pos, (const u8*)s.db.arena.p + to[k], ln[k], cudaMemcpyDeviceToHost);
+        pos += ln[k];
+    }
+    if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return DGC_E_CUDA; }
     return DGC_OK;
 }
 

@@ -102,6 +102,17 @@ struct PreAligned {
 // False on a blank line; throws M5Exception::FormatError like split_line.
 bool align_pre_line(const char* p, size_t n, PreAligned& out);
 
+// The dazcon form of a batch (include/dagcon_b200.h: dgc_daz_batch): overlaps with their trace points; the gapped
+// strings are built on the device.
+struct DazPayload {
+    uint32_t tspace = 0;
+    std::vector<uint32_t> tgt_aread, tgt_ovl_begin{0}, ovl_bread, ovl_comp, ovl_tlen;
+    std::vector<int32_t> ovl_abpos, ovl_aepos, ovl_bbpos, ovl_bepos;
+    std::vector<uint64_t> ovl_trace_off;
+    std::vector<uint8_t> trace;
+    dgc_daz_batch view() const;
+};
+
 // A packed batch in host memory (pinned when `pinned`), laid out as include/dagcon_b200.h: dgc_batch.
 class HostBatch {
 public:
@@ -125,6 +136,7 @@ public:
     bool has_backbone = false;
     std::vector<std::string> ids;   // Alignment::id of alns[0] per target
     uint64_t seq = 0;               // position in the input stream (batch number)
+    std::unique_ptr<DazPayload> daz;   // set: submit with dgc_submit_daz (n_targets and ids are filled, the arrays below unused)
 
     uint32_t* tgt_tlen = nullptr;
     uint32_t* tgt_aln_begin = nullptr;
@@ -161,6 +173,8 @@ struct ProgramOpts {
     bool sortCov = false;           // -x
     bool properOvls = false;        // -o
     std::set<int> targets;          // positional: limit consensus to these (1-based) target ids
+    bool hostRealign = false;       // --host-realign: rebuild the alignments on the host threads (dazzler's Compute_Trace_PTS)
+                                    // instead of on the device
     // dispatcher
     int gpus = 0;           // 0 = all visible devices
     size_t batchTargets = 256;          // a batch closes at this many targets or this much input text: small enough
@@ -183,6 +197,7 @@ struct BatchFeed {
     std::function<std::unique_ptr<HostBatch>(uint64_t seq)> take;   // nullptr = stream finished
     std::function<void(std::unique_ptr<HostBatch>)> recycle;
     std::function<bool()> failed;
+    const dgc_daz_db* daz_db = nullptr;   // dazcon with device realignment: uploaded to every handle before the first batch
 };
 int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunStats& stats, std::string& err, bool dazcon_header);
 
@@ -190,6 +205,8 @@ int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunSta
 // from its trace points, runs every target through the GPUs and writes ">id/n/b_e\nSEQ\n" records to `out`
 // (reference src/cpp/dazcon.cpp:38-120).
 int run_daz_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::string& err);
+// Test hook: the gapped strings the device builds for every selected overlap (text, see daz_provider.cpp).
+int daz_device_strings(const ProgramOpts& opts, std::string& text, std::string& err);
 // The dazcon front alone (scanner + realignment workers): every packed batch goes to `sink` in input order.
 typedef void (*BatchSink)(const HostBatch& batch, void* user);
 int pack_daz(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err);

@@ -39,6 +39,21 @@ void* dgh_daz_dump(const char* db, const char* las, unsigned min_cov, unsigned m
     }
     return d;
 }
+// The same overlaps through the DEVICE realignment (needs a GPU): "T id tlen n" / "A sid start q t" lines.
+void* dgh_daz_dump_device(const char* db, const char* las, unsigned min_cov, unsigned max_hits, int sort_cov, int proper,
+                          const int* targets, int n_targets) {
+    Dump* d = new Dump();
+    dgh::ProgramOpts po;
+    po.minCov = min_cov; po.alnFile = las; po.seqFile = db; po.maxHits = max_hits; po.sortCov = sort_cov != 0; po.properOvls = proper != 0;
+    for (int i = 0; i < n_targets; i++) po.targets.insert(targets[i]);
+    std::string err;
+    try {
+        if (dgh::daz_device_strings(po, d->text, err)) d->text = "ERROR " + err + "\n";
+    } catch (const std::exception& e) {
+        d->text = std::string("ERROR ") + e.what() + "\n";
+    }
+    return d;
+}
 const char* dgh_daz_text(void* h, uint64_t* n) { Dump* d = (Dump*)h; *n = d->text.size(); return d->text.data(); }
 void dgh_daz_free(void* h) { delete (Dump*)h; }
 

@@ -196,6 +196,21 @@ DazDb::~DazDb() { if (impl_->open) Close_DB(&impl_->db); }
 int DazDb::rlen(int read) const { return impl_->db.reads[read].rlen; }
 int DazDb::nreads() const { return impl_->db.nreads; }
 void* DazDb::handle() { return &impl_->db; }
+void DazDb::export_packed(std::vector<uint64_t>& boff, std::vector<uint32_t>& rlen, std::vector<uint8_t>& bases) {
+    HITS_DB& db = impl_->db;
+    boff.resize((size_t)db.nreads); rlen.resize((size_t)db.nreads);
+    for (int i = 0; i < db.nreads; i++) { boff[(size_t)i] = (uint64_t)db.reads[i].boff; rlen[(size_t)i] = (uint32_t)db.reads[i].rlen; }
+    const std::string path = std::string(db.path) + ".bps";     // HITS_DB.path = "<dir>/.<root>" (DB.c Open_DB)
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) throw PacBio::DagCon::IOException("cannot open " + path);
+    fseeko(f, 0, SEEK_END);
+    const off_t n = ftello(f);
+    fseeko(f, 0, SEEK_SET);
+    bases.resize((size_t)n);
+    const size_t got = n ? fread(bases.data(), 1, (size_t)n, f) : 0;
+    fclose(f);
+    if (got != (size_t)n) throw PacBio::DagCon::IOException("short read on " + path);
+}
 
 // ------------------------------------------------------------------------------------------ realignment (host form)
 struct Realizer::Impl {
@@ -302,6 +317,7 @@ void Realizer::realize(const LasRec& rec, int alen, int blen, dagcon::Alignment&
 }
 
 }  // namespace daz
+
 }  // namespace dgh
 
 // ------------------------------------------------------------------------------------------ the reference-shaped provider
@@ -395,7 +411,53 @@ struct DazFront {
     std::atomic<int> live{0};
     size_t pool_max = 0;
 
+    // device realignment (dgc_submit_daz): the batches carry overlaps + trace points instead of strings
+    bool device_realign = false;
+    int tbytes = 1;
+    std::vector<uint64_t> db_boff;
+    std::vector<uint32_t> db_rlen;
+    std::vector<uint8_t> db_bases;
+    dgc_daz_db db_view{};
+
     DazFront(const ProgramOpts& o, bool pin, RunStats& st) : opts(o), pinned(pin), stats(st) {}
+
+    // Can the device take this unit?  Same conditions as the library's own validation: byte-wide trace values, a
+    // trace of one pair per trace-spacing block of A, the last block's B stretch within the kernel's limit.
+    bool unit_device_ok(const DazUnit& u) const {
+        if (!device_realign || tbytes != 1 || tspace <= 0 || tspace > 125) return false;
+        for (const auto& p : u.piles)
+            for (const auto& r : p.recs) {
+                if (r.tlen < 2 || (r.tlen & 1)) return false;
+                const int want = r.aepos / tspace - r.abpos / tspace + ((r.aepos % tspace) ? 1 : 0);
+                if (r.tlen / 2 != (want ? want : 1)) return false;
+                long sb = r.bbpos;
+                for (int i = 0; i + 1 < r.tlen / 2; i++) sb += r.trace[(size_t)(2 * i + 1)];
+                if (sb > r.bepos || r.bepos - sb > 256) return false;
+                if (r.abpos < 0 || r.aepos < r.abpos || r.aepos > p.length || r.bbpos < 0 || r.bepos < r.bbpos) return false;
+            }
+        return true;
+    }
+    void pack_device(const DazUnit& u, HostBatch& hb) {
+        if (!hb.daz) hb.daz.reset(new DazPayload());
+        DazPayload& z = *hb.daz;
+        z = DazPayload();
+        z.tspace = (uint32_t)tspace;
+        for (const auto& p : u.piles) {
+            z.tgt_aread.push_back((uint32_t)p.aread);
+            hb.ids.push_back(std::to_string(p.aread + 1));
+            for (const auto& r : p.recs) {
+                z.ovl_bread.push_back((uint32_t)r.bread);
+                z.ovl_comp.push_back(r.flags & 1u);
+                z.ovl_abpos.push_back(r.abpos); z.ovl_aepos.push_back(r.aepos); z.ovl_bbpos.push_back(r.bbpos); z.ovl_bepos.push_back(r.bepos);
+                z.ovl_trace_off.push_back(z.trace.size());
+                z.ovl_tlen.push_back((uint32_t)r.tlen);
+                for (int i = 0; i < r.tlen; i++) z.trace.push_back((uint8_t)r.trace[(size_t)i]);
+            }
+            z.tgt_ovl_begin.push_back((uint32_t)z.ovl_bread.size());
+        }
+        hb.n_targets = (uint32_t)u.piles.size();
+        hb.n_alns = (uint32_t)z.ovl_bread.size();
+    }
 
     void fail(int code, const std::string& msg) {
         std::lock_guard<std::mutex> lk(err_mu);
@@ -411,7 +473,15 @@ struct DazFront {
         try {
             LasFile probe(opts.alnFile);
             tspace = probe.tspace;
+            tbytes = probe.tbytes;
             lens.reset(new DazDb(opts.seqFile));
+            device_realign = !opts.hostRealign && pinned && tbytes == 1;   // pack_daz (tests, bench) asks for strings
+            if (device_realign) {
+                lens->export_packed(db_boff, db_rlen, db_bases);
+                db_view.n_reads = (uint32_t)db_rlen.size();
+                db_view.read_boff = db_boff.data(); db_view.read_len = db_rlen.data();
+                db_view.bases = db_bases.data(); db_view.bases_bytes = db_bases.size();
+            }
         } catch (const std::exception& e) { err = e.what(); return DGC_E_INVALID; }
         return 0;
     }
@@ -463,8 +533,10 @@ struct DazFront {
         live = nw;
         for (int w = 0; w < nw; w++) {
             workers.emplace_back([this] {
-                std::unique_ptr<Realizer> rz;
-                try { rz.reset(new Realizer(opts.seqFile, tspace)); } catch (const std::exception& e) { fail(DGC_E_INVALID, e.what()); }
+                std::unique_ptr<Realizer> rz;   // the host form: one dazzler DB handle + Work_Data per worker, made on first use
+                auto need_rz = [&] {
+                    if (!rz) try { rz.reset(new Realizer(opts.seqFile, tspace)); } catch (const std::exception& e) { fail(DGC_E_INVALID, e.what()); }
+                };
                 std::vector<dagcon::Alignment> alns;
                 std::string tseq;
                 for (;;) {
@@ -479,9 +551,17 @@ struct DazFront {
                     try {
                         hb->clear();
                         hb->seq = u->seq;
+                        hb->daz.reset();
+                        if (unit_device_ok(*u)) {
+                            pack_device(*u, *hb);
+                            u.reset();
+                            outbox.put(std::move(hb));
+                            continue;
+                        }
                         size_t nal = 0, bb = 0;
                         for (auto& p : u->piles) { nal += p.recs.size(); bb += (size_t)p.length + 16; }
                         hb->reserve(2 * (u->cols + u->cols / 6) + 64 * nal + bb, nal, u->piles.size());
+                        need_rz();
                         if (rz) for (auto& p : u->piles) {
                             alns.resize(p.recs.size());
                             for (size_t k = 0; k < p.recs.size(); k++) rz->realize(p.recs[k], p.length, p.blens[k], alns[k]);
@@ -507,6 +587,56 @@ struct DazFront {
 };
 
 }  // namespace
+
+// Test hook: what the DEVICE writes for every selected overlap (dgc_debug_daz_strings), as "A sid start q t" lines
+// under "T id tlen n" headers -- the host provider's dump format without the target sequence.
+int daz_device_strings(const ProgramOpts& opts, std::string& text, std::string& err) {
+    RunStats st;
+    DazFront fr(opts, true, st);
+    int rc = fr.open(err);
+    if (rc) return rc;
+    if (!fr.device_realign) { err = "this LAS cannot take the device path (two-byte trace values)"; return DGC_E_DAZ; }
+    dgc_opts o{};
+    o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = 0;
+    dgc_handle* h = nullptr;
+    if ((rc = dgc_create(&o, &h)) != 0) { err = dgc_last_error(nullptr); return rc; }
+    if ((rc = dgc_daz_set_db(h, &fr.db_view)) != 0) { err = dgc_last_error(h); dgc_destroy(h); return rc; }
+    PileScanner scan(opts.alnFile, *fr.lens, opts.properOvls);
+    Pile pile;
+    std::vector<const LasRec*> recs;
+    std::vector<int> blens;
+    std::vector<uint8_t> q, t;
+    std::vector<uint64_t> off;
+    std::vector<uint32_t> len;
+    while (scan.next(pile)) {
+        if (!opts.targets.empty() && !opts.targets.count(pile.aread + 1)) continue;
+        pile.select(opts.maxHits, opts.sortCov, recs, blens);
+        if (recs.size() < opts.minCov) continue;
+        DazUnit u;
+        SelPile sp;
+        sp.aread = pile.aread; sp.length = pile.length; sp.blens = blens;
+        for (const LasRec* r : recs) sp.recs.push_back(*r);
+        u.piles.push_back(std::move(sp));
+        if (!fr.unit_device_ok(u)) { err = "a pile the device path cannot take"; dgc_destroy(h); return DGC_E_DAZ; }
+        HostBatch hb(false, 0, 0, 0);
+        fr.pack_device(u, hb);
+        const dgc_daz_batch zb = hb.daz->view();
+        size_t cap = 0;
+        for (const LasRec* r : recs) { cap += (size_t)(r->aepos - r->abpos + 1); for (int i = 0; i < r->tlen; i += 2) cap += r->trace[(size_t)i]; }
+        q.resize(cap + 16); t.resize(cap + 16); off.resize(recs.size() + 1); len.resize(recs.size() + 1);
+        if ((rc = dgc_debug_daz_strings(h, &zb, q.data(), t.data(), cap + 16, off.data(), len.data())) != 0) { err = dgc_last_error(h); dgc_destroy(h); return rc; }
+        text += "T " + std::to_string(pile.aread + 1) + " " + std::to_string(pile.length) + " " + std::to_string(recs.size()) + "\n";
+        for (size_t k = 0; k < recs.size(); k++) {
+            text += "A " + std::to_string(recs[k]->bread + 1) + " " + std::to_string(recs[k]->abpos + 1) + " ";
+            text.append((const char*)q.data() + off[k], len[k]);
+            text.push_back(' ');
+            text.append((const char*)t.data() + off[k], len[k]);
+            text.push_back('\n');
+        }
+    }
+    dgc_destroy(h);
+    return 0;
+}
 
 int pack_daz(const ProgramOpts& opts, bool pinned, BatchSink sink, void* user, RunStats& stats, std::string& err) {
     DazFront fr(opts, pinned, stats);
@@ -539,6 +669,7 @@ int run_daz_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::s
     feed.take = [&](uint64_t seq) { return fr.outbox.take(seq); };
     feed.recycle = [&](std::unique_ptr<HostBatch> hb) { fr.free_batches.push(std::move(hb)); };
     feed.failed = [&] { return fr.failed(); };
+    if (fr.device_realign) feed.daz_db = &fr.db_view;
     rc = dispatch_batches(opts, feed, out, stats, err, true);
     fr.stop();
     if (!rc && fr.frc) { rc = fr.frc; err = fr.ferr; }

@@ -50,6 +50,9 @@ public:
     int rlen(int read) const override;
     int nreads() const;
     void* handle();   // HITS_DB*
+    // the whole trimmed DB as the device wants it (dgc_daz_db): per read its byte offset in the .bps file and its
+    // length, plus the .bps file itself
+    void export_packed(std::vector<uint64_t>& boff, std::vector<uint32_t>& rlen, std::vector<uint8_t>& bases);
 
 private:
     struct Impl;

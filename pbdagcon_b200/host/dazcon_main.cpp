@@ -32,6 +32,8 @@ void usage(FILE* f) {
           "   --gpus <int>                    GPUs to use (default: all visible)\n"
           "   --batch-targets <int>, --batch-mb <int>   targets / MiB of alignment columns per GPU batch\n"
           "   --stats                         print a JSON throughput line on stderr\n"
+          "   --host-realign                  rebuild the alignments from the trace points on the host threads (dazzler's\n"
+          "                                   Compute_Trace_PTS) instead of on the GPU\n"
           "   <list of ints>                  Limit consensus to list of target ids\n\n"
           "   PBI consensus module, B200 build\n",
           f);
@@ -66,6 +68,7 @@ int main(int argc, char** argv) {
         if (a == "-x" || a == "--coverage-sort") { o.sortCov = true; continue; }
         if (a == "-o" || a == "--only-proper-overlaps") { o.properOvls = true; continue; }
         if (a == "--stats") { o.stats = true; continue; }
+        if (a == "--host-realign") { o.hostRealign = true; continue; }
         // combined switches as TCLAP accepts them: -ox, -xo, -vox ...
         if (a.size() > 2 && a[1] != '-' && a.find_first_not_of("vxo", 1) == std::string::npos) {
             for (size_t k = 1; k < a.size(); k++) {

@@ -363,6 +363,10 @@ int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunSta
         o.min_cov = (uint32_t)opts.minCov; o.min_len = (uint32_t)opts.minLen; o.trim = opts.trim; o.device = g % ndev;
         const int rc = dgc_create(&o, &hs[(size_t)g]);
         if (rc) { err = std::string("dgc_create: ") + dgc_last_error(nullptr); destroy_all(); return rc; }
+        if (feed.daz_db) {
+            const int rd = dgc_daz_set_db(hs[(size_t)g], feed.daz_db);
+            if (rd) { err = std::string("dgc_daz_set_db: ") + dgc_last_error(hs[(size_t)g]); destroy_all(); return rd; }
+        }
     }
     if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s %d GPU handle(s) ready\n", dazcon_header ? "dazcon" : "pbdagcon", since(t0), G);
 
@@ -416,10 +420,11 @@ int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunSta
         if (rc || feed.failed()) { feed.recycle(std::move(hb)); continue; }
         const int g = (int)(seq % (uint64_t)G);
         while (on_gpu[(size_t)g] >= DGC_MAX_INFLIGHT) collect_oldest();
-        const dgc_batch b = hb->view();
-        // the dgc_batch struct is read during submit only; the arrays it points to stay alive in `inflight`
+        // the batch struct is read during submit only; the arrays it points to stay alive in `inflight`
         if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s submit batch %llu (%u targets, %.1f MB) to GPU %d\n", prog, since(t0), (unsigned long long)seq, hb->n_targets, hb->arena_bytes / 1e6, g);
-        const int c = dgc_submit(hs[(size_t)g], &b);
+        int c;
+        if (hb->daz) { const dgc_daz_batch zb = hb->daz->view(); c = dgc_submit_daz(hs[(size_t)g], &zb); }
+        else { const dgc_batch b = hb->view(); c = dgc_submit(hs[(size_t)g], &b); }
         if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); feed.recycle(std::move(hb)); continue; }
         on_gpu[(size_t)g]++;
         stats.batches++;

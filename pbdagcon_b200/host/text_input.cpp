@@ -325,6 +325,19 @@ dgc_batch HostBatch::view() const {
     return b;
 }
 
+dgc_daz_batch DazPayload::view() const {
+    dgc_daz_batch b{};
+    b.n_targets = (uint32_t)tgt_aread.size();
+    b.n_ovls = (uint32_t)ovl_bread.size();
+    b.tspace = tspace;
+    b.tgt_aread = tgt_aread.data(); b.tgt_ovl_begin = tgt_ovl_begin.data();
+    b.ovl_bread = ovl_bread.data(); b.ovl_comp = ovl_comp.data();
+    b.ovl_abpos = ovl_abpos.data(); b.ovl_aepos = ovl_aepos.data(); b.ovl_bbpos = ovl_bbpos.data(); b.ovl_bepos = ovl_bepos.data();
+    b.ovl_trace_off = ovl_trace_off.data(); b.ovl_tlen = ovl_tlen.data();
+    b.trace = trace.data(); b.trace_bytes = trace.size();
+    return b;
+}
+
 }  // namespace dgh
 
 // ------------------------------------------------------------------------------------------ provider

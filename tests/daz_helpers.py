@@ -84,6 +84,18 @@ class _Daz:
 
 def host():
     d = _Daz(HOST_SO, "dgh_daz_")
+    f = d.lib.dgh_daz_dump_device
+    f.restype = C.c_void_p
+    f.argtypes = [C.c_char_p, C.c_char_p, C.c_uint, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int]
+
+    def dump_device(db, las, min_cov=6, max_hits=85, sort_cov=0, proper=0, targets=()):
+        arr = (C.c_int * len(targets))(*targets)
+        h = f(str(db).encode(), str(las).encode(), min_cov, max_hits, sort_cov, proper, arr, len(targets))
+        n = C.c_uint64()
+        s = C.string_at(d.lib.dgh_daz_text(h, C.byref(n)), n.value)
+        d.lib.dgh_daz_free(h)
+        return s
+    d.dump_device = dump_device
     d.lib.dgh_daz_group_hits.restype = C.c_int
     d.lib.dgh_daz_group_hits.argtypes = [C.POINTER(C.c_int), C.c_int]
     return d

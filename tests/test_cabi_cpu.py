@@ -35,7 +35,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(api.Opts) == 32
     assert C.sizeof(api.CBatch) == 8 + 8 * 8 + 8
     assert C.sizeof(api.CResults) == 8 + 8 * 7 + 8
-    assert C.sizeof(api.Timings) == 10 * 4 + 2 * 4 + 4 * 8
+    assert C.sizeof(api.Timings) == 10 * 4 + 2 * 4 + 4 * 8 + 2 * 4
 
 
 def test_no_cpu_fallback(lib_path):

@@ -69,3 +69,28 @@ def test_dazcon_generated_pair_against_reference(tmp_path):
     assert [int(h.split(b"/")[1]) for h in heads] == list(range(len(heads)))
     ids = [int(h.split(b"/")[0][1:]) for h in heads]
     assert ids == sorted(ids)
+
+
+def test_device_realignment_strings_equal_host_provider():
+    """the gapped strings the DEVICE builds from the trace points (k_daz_iter = iter_np per segment,
+    k_daz_emit = decodeAlignment) against the host provider, which runs the dazzler library's own Compute_Trace_PTS and
+    is itself pinned to the reference provider (tests/test_daz_cpu.py): every overlap, byte for byte."""
+    h = dh.host()
+    for kw in (dict(), dict(min_cov=2, max_hits=6, sort_cov=1, proper=1)):
+        dev = h.dump_device(dh.DB, dh.LAS, **kw)
+        assert not dev.startswith(b"ERROR"), dev[:200]
+        host = dh.parse_dump(h.dump(str(dh.DB), str(dh.LAS), **kw))
+        got = dh.parse_dump(b"\n".join(ln + b" ." if ln.startswith(b"T ") else ln for ln in dev.split(b"\n")))
+        assert len(got) == len(host) and len(host) > 100
+        n = 0
+        for (hid, hl, _, ha), (gid, gl, _, ga) in zip(host, got):
+            assert (hid, hl) == (gid, gl)
+            assert ha == ga, f"target {hid}"
+            n += len(ha)
+        assert n > 1000
+
+
+def test_dazcon_device_and_host_realignment_print_the_same_fasta():
+    a = run(dh.DAZCON, ["-j", "4", "-s", str(dh.DB), "-a", str(dh.LAS)])
+    b = run(dh.DAZCON, ["-j", "4", "-s", str(dh.DB), "-a", str(dh.LAS), "--host-realign"])
+    assert a == b and a.count(b">") > 100
