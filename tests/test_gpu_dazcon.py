@@ -87,7 +87,7 @@ def test_device_realignment_strings_equal_host_provider():
             assert (hid, hl) == (gid, gl)
             assert ha == ga, f"target {hid}"
             n += len(ha)
-        assert n > 1000
+        assert n > 500
 
 
 def test_dazcon_device_and_host_realignment_print_the_same_fasta():
