@@ -497,14 +497,17 @@ struct DazFront {
                 std::vector<int> blens;
                 std::unique_ptr<DazUnit> u(new DazUnit());
                 uint64_t seq = 0;
-                // early units are small so that the GPUs start at once; later ones grow to opts.batchTargets
-                size_t want = std::min<size_t>(opts.batchTargets, 32);
+                // Unit sizes.  A batch costs the latency of the longest dependent chain of the graph sweeps however few
+                // targets it holds, so batches want to be large.  With the realignment on the device the scanner is the
+                // only host work per target and a large unit is cut in milliseconds: start at 1024 targets.  With the
+                // dazzler library rebuilding the alignments on the host threads, small early units start the GPUs sooner.
+                size_t want = std::min<size_t>(opts.batchTargets, device_realign ? 1024 : 32);
                 auto flush = [&] {
                     if (u->piles.empty()) return;
                     u->seq = seq++;
                     units.push(std::move(u));
                     u.reset(new DazUnit());
-                    want = std::min(opts.batchTargets, want * 2);
+                    want = std::min(opts.batchTargets, want * (device_realign ? 4 : 2));
                 };
                 while (scan.next(pile)) {
                     stats.targets_in++;

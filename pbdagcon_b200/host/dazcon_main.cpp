@@ -51,7 +51,8 @@ bool parse_ull(const char* s, unsigned long long& v) {
 int main(int argc, char** argv) {
     dgh::ProgramOpts o;
     o.trim = 10;            // dazcon's default (dazcon.cpp:143-146); pbdagcon's is 50
-    o.batchTargets = 512;
+    o.batchTargets = 4096;
+    o.batchBytes = 2048ull << 20;
     bool only_positional = false;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
