@@ -49,8 +49,6 @@ extern "C" {
 #define DGC_F_SINGLE 8u       /* consensus(minWeight) -> one longest run (AlnGraphBoost.cpp:285-325)
                                  instead of consensus(seqs,minWeight,minLen) (:327-373) */
 #define DGC_F_SPLIT_SWEEPS 512u /* tuning/diagnostic: mergeNodes and bestPath as two launches (per-kernel timings) */
-#define DGC_F_THREAD_SWEEPS 1024u /* tuning: the graph sweeps always run one THREAD per target (default: chosen by the chunk's size) */
-#define DGC_F_WARP_SWEEPS 2048u  /* tuning: the graph sweeps always run one WARP per target */
 #define DGC_F_NO_PREFETCH 256u /* tuning/diagnostic: the graph sweeps do not prefetch vertex records (results identical) */
 
 /* Replaces ProgramOpts (src/cpp/ProgramOpts.hpp:8-36) for this path. */

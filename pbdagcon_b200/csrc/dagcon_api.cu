@@ -158,7 +158,6 @@ struct dgc_handle {
     // staged uploads (run_staged): piece size and the smallest arena worth staging; DGC_STAGE_PIECE_BYTES /
     // DGC_STAGE_MIN_BYTES override them (tests stage tiny batches)
     uint64_t stage_piece_bytes = 384ull << 20, stage_min_bytes = 64ull << 20;
-    uint32_t thread_sweep_min = 0xFFFFFFFFu;  // chunks of at least this many targets sweep one thread per target (DGC_THREAD_SWEEP_MIN)
     std::string err;
     Slot slots[NSLOT];
     uint64_t submitted = 0, collected = 0;
@@ -397,15 +396,7 @@ int launch_serial(Slot& s, dgc_dbatch& db, const Chunk& c, int stop_after) {
     }
     const uint32_t warps_per_block = WARP_KERNEL_THREADS / 32;   // one warp per target
     const uint32_t grid = (c.count + warps_per_block - 1) / warps_per_block;
-    // one thread per target when the chunk holds enough targets to keep the SMs busy that way (see graph_rec.cuh)
-    const bool by_thread = !(o.flags & DGC_F_WARP_SWEEPS) && ((o.flags & DGC_F_THREAD_SWEEPS) || c.count >= s.h->thread_sweep_min);
-    if (stop_after >= 2 && by_thread && !(o.flags & DGC_F_SPLIT_SWEEPS)) {
-        span_begin(s, PH_MERGE);
-        k_merge_best_t<<<(c.count + THREAD_KERNEL_THREADS - 1) / THREAD_KERNEL_THREADS, THREAD_KERNEL_THREADS, 0, st>>>(sa);
-        s.tm.launches++;
-        CU(cudaGetLastError());
-        span_end(s);
-    } else if (stop_after >= 2 && !(o.flags & (DGC_F_NO_MERGE | DGC_F_SPLIT_SWEEPS))) {
+    if (stop_after >= 2 && !(o.flags & (DGC_F_NO_MERGE | DGC_F_SPLIT_SWEEPS))) {
         span_begin(s, PH_MERGE);  // both sweeps in one launch; reported as ms_merge
         k_merge_best2<<<grid, WARP_KERNEL_THREADS, 0, st>>>(sa);
         s.tm.launches++;
@@ -1267,7 +1258,6 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
     if (const char* e1 = getenv("DGC_STAGE_PIECE_BYTES")) h->stage_piece_bytes = std::max<uint64_t>(1, strtoull(e1, nullptr, 10));
     if (const char* e3 = getenv("DGC_TEST_TINY_POOL")) g_tiny_pool = e3[0] == '1';
     if (const char* e2 = getenv("DGC_STAGE_MIN_BYTES")) h->stage_min_bytes = strtoull(e2, nullptr, 10);
-    if (const char* e5 = getenv("DGC_THREAD_SWEEP_MIN")) h->thread_sweep_min = (uint32_t)strtoull(e5, nullptr, 10);
     {   // opt in to large dynamic shared memory for the build kernel (static use is ~4.2 KB)
         size_t optin = prop.sharedMemPerBlockOptin > 8192 ? prop.sharedMemPerBlockOptin - 8192 : 0;
         // 74 KB = three blocks per SM.  Measured on B200: 8 kb backbones 89 ms in shared memory vs 103 ms in gacc;

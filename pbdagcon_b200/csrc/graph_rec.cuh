@@ -994,49 +994,6 @@ __device__ __forceinline__ u32 f2ord(float f) {  // order-preserving map float -
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-// walk the best path from enter and cut it into min-weight runs (consensus :285-373); one thread
-__device__ __noinline__ void walk_best_path(const Serial2Args& a, const u32 t, const GV& g) {
-    const u32 L = a.tgt_tlen[t], ENTER = 0, EXIT = 2 * (L + 1), nV = a.tgt_nv[t];
-    u8* cons = a.cons + a.cons_off[t];
-    int* fr = a.frags + 2 * a.frag_off[t];
-    const u32 fcap = a.frag_cap[t];
-    const u32 eb = n_base(gv_hdr(g, ENTER)->bfv), xb = n_base(gv_hdr(g, EXIT)->bfv);
-    const int minw = (int)a.min_weight;
-    const bool single = a.flags & F_SINGLE;
-    int offs = 0, idx = 0, best_offs = 0, length = 0;
-    bool met = false;
-    u32 nfrag = 0, steps = 0, prev = ENTER, status = T_OK;
-    for (;;) {
-        const Hdr hp = *gv_hdr(g, prev);
-        const u32 b = hp.bfv & 0xFFu;
-        const int w = hp.weight;
-        if (b != eb && b != xb) {
-            cons[idx] = (u8)b;
-            if (!met && w >= minw) { offs = idx; met = true; }
-            else if (met && w < minw) {
-                met = false;
-                if (single) { if (idx - offs > length) { best_offs = offs; length = idx - offs; } }
-                else if ((u32)(idx - offs) >= a.min_len) {
-                    if (nfrag < fcap) { fr[2 * nfrag] = offs; fr[2 * nfrag + 1] = idx; nfrag++; } else status = T_INTERNAL;
-                }
-            }
-            idx++;
-        }
-        if (!(hp.bfv & (NF_SCORED << 8)) || hp.best == NIL) break;
-        prev = hp.best;
-        if (++steps > nV) { status = T_INTERNAL; break; }
-    }
-    if (single) {
-        if (met && idx - offs > length) { best_offs = offs; length = idx - offs; }
-        fr[0] = best_offs; fr[1] = best_offs + length; nfrag = 1;
-    } else if (met && (u32)(idx - offs) >= a.min_len) {
-        if (nfrag < fcap) { fr[2 * nfrag] = offs; fr[2 * nfrag + 1] = idx; nfrag++; } else status = T_INTERNAL;
-    }
-    a.tgt_cons_len[t] = (u32)idx;
-    a.tgt_nfrag[t] = nfrag;
-    if (status != T_OK) { a.tgt_status[t] = status; a.tgt_nfrag[t] = 0; }
-}
-
 __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, const T2Ctx& c) {
     const GV& g = c.g;
     const u32 lane = threadIdx.x & 31;
@@ -1129,7 +1086,45 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
         head = nx;
     }
     if (lane != 0) return;
-    walk_best_path(a, t, g);
+    // walk the best path and cut it into min-weight runs (consensus :285-373)
+    u8* cons = a.cons + a.cons_off[t];
+    int* fr = a.frags + 2 * a.frag_off[t];
+    const u32 fcap = a.frag_cap[t];
+    const u32 eb = n_base(gv_hdr(g, ENTER)->bfv), xb = n_base(gv_hdr(g, EXIT)->bfv);
+    const int minw = (int)a.min_weight;
+    const bool single = a.flags & F_SINGLE;
+    int offs = 0, idx = 0, best_offs = 0, length = 0;
+    bool met = false;
+    u32 nfrag = 0, steps = 0, prev = ENTER, status = T_OK;
+    for (;;) {
+        const Hdr hp = *gv_hdr(g, prev);
+        const u32 b = hp.bfv & 0xFFu;
+        const int w = hp.weight;
+        if (b != eb && b != xb) {
+            cons[idx] = (u8)b;
+            if (!met && w >= minw) { offs = idx; met = true; }
+            else if (met && w < minw) {
+                met = false;
+                if (single) { if (idx - offs > length) { best_offs = offs; length = idx - offs; } }
+                else if ((u32)(idx - offs) >= a.min_len) {
+                    if (nfrag < fcap) { fr[2 * nfrag] = offs; fr[2 * nfrag + 1] = idx; nfrag++; } else status = T_INTERNAL;
+                }
+            }
+            idx++;
+        }
+        if (!(hp.bfv & (NF_SCORED << 8)) || hp.best == NIL) break;
+        prev = hp.best;
+        if (++steps > nV) { status = T_INTERNAL; break; }
+    }
+    if (single) {
+        if (met && idx - offs > length) { best_offs = offs; length = idx - offs; }
+        fr[0] = best_offs; fr[1] = best_offs + length; nfrag = 1;
+    } else if (met && (u32)(idx - offs) >= a.min_len) {
+        if (nfrag < fcap) { fr[2 * nfrag] = offs; fr[2 * nfrag + 1] = idx; nfrag++; } else status = T_INTERNAL;
+    }
+    a.tgt_cons_len[t] = (u32)idx;
+    a.tgt_nfrag[t] = nfrag;
+    if (status != T_OK) { a.tgt_status[t] = status; a.tgt_nfrag[t] = 0; }
 }
 __global__ void __launch_bounds__(WARP_KERNEL_THREADS) k_best_path2(Serial2Args a) {
     u32 t;
@@ -1147,142 +1142,4 @@ __global__ void __launch_bounds__(WARP_KERNEL_THREADS, MERGE_MIN_BLOCKS) k_merge
     if (!warp2_setup(a, t, c)) return;
     if (merge_sweep(a, t, c) != T_OK) return;
     best_sweep(a, t, c);
-}
-
-// ------------------------------------------------------------------------------------------
-// K3 + K4, one THREAD per target.  The warp-per-target sweeps above spend a warp instruction where one lane's worth
-// of work is to be done: a pop costs ~180 (mergeNodes) / ~140 (bestPath) warp instructions at 16 of 32 lanes, and at
-// the bench's 10 000 targets the launch is bound by instruction issue (53 % issue-active), not by memory.  Here every
-// lane walks its own target with the scalar list primitives (the same ones lane 0 runs in the slow paths above), so a
-// warp instruction advances up to 32 targets; divergence between the lanes' code paths costs a factor of a few, not
-// 32.  One launch then holds every target of a chunk in ONE wave (10 000 targets = 313 warps on 148 SMs) and runs at
-// the latency of the longest chain.  Few targets per launch favour the warp form (its lanes fetch a vertex's
-// neighbours at once); the dispatcher picks by the number of targets in the chunk.
-__device__ __forceinline__ bool thread_setup(const Serial2Args& a, u32& t, T2Ctx& c) {
-    const u32 idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.count) return false;
-    t = a.order ? a.order[a.first + idx] : a.first + idx;
-    if (a.tgt_status[t] != T_OK) return false;
-    c.g.base = a.rec + (size_t)REC_UNIT * a.rec_off[t];
-    c.g.nbb = a.tgt_tlen[t] + 2;
-    const u32 pool_begin = 16u * (c.g.nbb + a.tgt_V[t]);
-    c.g.pool_top = a.tgt_pool_top[t];
-    c.g.pool_end = pool_begin + a.pool_cap[t];
-    c.g.status = T_OK;
-    c.g.pool_failed = 0;
-    c.g.nunits = (a.flags & F_NO_PREFETCH) ? 0u : pool_begin / 16u;
-    c.S = a.gscratch + a.gscratch_off[t];
-    c.scap = a.gscratch_cap[t];
-    return true;
-}
-
-// mergeNodes :129-160
-__device__ __forceinline__ u32 merge_sweep_t(const Serial2Args& a, const u32 t, T2Ctx& c) {
-    GV& g = c.g;
-    u32 head = 0, tail = 0;
-    {
-        Hdr* he = gv_hdr(g, 0);
-        he->best = NIL;
-        he->bfv |= NF_QUEUED << 8;
-    }
-#pragma unroll 1
-    while (head != NIL && g.status == T_OK) {
-        const u32 u = head;
-        Hdr* pu = gv_hdr(g, u);
-        u32 deg = pu->deg;
-        if ((deg & 0xFFFFu) >= 2) { m2_merge_in(c, u); deg = pu->deg; }
-        if ((deg >> 16) >= 2) { m2_merge_out_generic(c, u); deg = pu->deg; }
-        const u32 nout = deg >> 16;
-        OSlot* o = gv_out(g, pu->out_ptr);
-#pragma unroll 1
-        for (u32 i = 0; i < nout; i++) {   // :146-158: mark the out-edges visited; a target whose in-edges are all visited is enqueued
-            const OSlot s = o[i];
-            u8* rv = g.base + (size_t)s.dst * REC_UNIT;
-            uint2 d = *(const uint2*)rv;
-#ifndef GV_NO_PREFETCH
-            if (g.nunits) {
-                const OSlot s0 = *(const OSlot*)(rv + REC_OUT_OFF);   // the successor's first out-slot (inline position)
-                if (d.y >> 16) gv_prefetch_rec(g, s0.dst);
-            }
-#endif
-            const u32 was = d.x;
-            if (!(s.cv & VISBIT)) { o[i].cv = s.cv | VISBIT; d.x += 0x10000u; }
-            if ((d.x >> 16) == (d.y & 0xFFFFu)) {
-                if (d.x & (NF_QUEUED << 8)) { g.status = T_INTERNAL; break; }
-                d.x |= NF_QUEUED << 8;
-                ((Hdr*)rv)->bfv = d.x;
-                gv_hdr(g, tail)->best = s.dst;
-                tail = s.dst;
-            } else if (d.x != was) {
-                ((Hdr*)rv)->bfv = d.x;
-            }
-        }
-        head = pu->best;
-    }
-    a.tgt_pool_top[t] = g.pool_top;
-    u32 status = g.status;
-    if (g.pool_failed) status = T_POOL;
-    if (status != T_OK) a.tgt_status[t] = status;
-    return status;
-}
-
-// bestPath :375-459
-__device__ __forceinline__ void best_sweep_t(const Serial2Args& a, const u32 t, const T2Ctx& c) {
-    const GV& g = c.g;
-    const u32 L = a.tgt_tlen[t], EXIT = 2 * (L + 1);
-    u32 head = EXIT, tail = EXIT;
-    gv_hdr(g, EXIT)->best = NIL;
-#pragma unroll 1
-    while (head != NIL) {
-        const u32 n = head;
-        Hdr* pn = gv_hdr(g, n);
-        const Hdr hn = *pn;
-        const u32 nout = hn.deg >> 16, nin = hn.deg & 0xFFFFu;
-        float best_score = -FLT_MAX;
-        u32 best_dst = NIL;
-        const OSlot* o = gv_out(g, hn.out_ptr);
-#pragma unroll 1
-        for (u32 i = 0; i < nout; i++) {
-            const OSlot s = o[i];
-            const Hdr hd = *gv_hdr(g, s.dst);
-            float ns;
-            if ((hd.bfv & (NF_BACKBONE << 8)) && hd.weight == 1) ns = __fsub_rn(hd.score, 10.0f);
-            else ns = __fadd_rn(__fsub_rn((float)(int)(s.cv & ~VISBIT), __fmul_rn((float)hd.cov, 0.5f)), hd.score);
-            if (ns > best_score) { best_score = ns; best_dst = s.dst; }   // strict >: the first maximum in list order stays
-        }
-        const u32* in = gv_in(g, hn.in_ptr);
-#pragma unroll 1
-        for (u32 i = 0; i < nin; i++) {
-            const u32 s = in[i];
-            Hdr* hs = gv_hdr(g, s);
-            const u32 sdeg = hs->deg;
-            const u32 k = (u32)(hs->cnt + 1);
-#ifndef GV_NO_PREFETCH
-            if (g.nunits && (sdeg & 0xFFFFu)) gv_prefetch_rec(g, *(const u32*)((const u8*)hs + REC_IN_OFF));
-#endif
-            hs->cnt = (int)k;
-            if (k == (sdeg >> 16)) {
-                hs->best = NIL;
-                gv_hdr(g, tail)->best = s;
-                tail = s;
-            }
-        }
-        const u32 nx = pn->best;
-        pn->score = best_dst != NIL ? best_score : 0.0f;
-        pn->best = best_dst;
-        pn->bfv = hn.bfv | (NF_SCORED << 8);
-        head = nx;
-    }
-    walk_best_path(a, t, g);
-}
-
-#ifndef THREAD_KERNEL_THREADS
-#define THREAD_KERNEL_THREADS 64
-#endif
-__global__ void __launch_bounds__(THREAD_KERNEL_THREADS) k_merge_best_t(Serial2Args a) {
-    u32 t;
-    T2Ctx c;
-    if (!thread_setup(a, t, c)) return;
-    if (!(a.flags & F_NO_MERGE) && merge_sweep_t(a, t, c) != T_OK) return;
-    best_sweep_t(a, t, c);
 }
