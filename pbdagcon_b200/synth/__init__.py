@@ -39,6 +39,7 @@ def _load():
         _lib.dgs_write_m5.restype = C.c_int64
         _lib.dgs_write_m5.argtypes = [C.POINTER(_Params), C.c_uint64, C.c_uint32, C.c_char_p]
         _lib.dgs_alns_per_target.argtypes = [C.POINTER(_Params)]
+        _lib.dgs_backbone.argtypes = [C.POINTER(_Params), C.c_uint64, C.c_char_p]
     return _lib
 
 
@@ -109,6 +110,15 @@ def write_m5(seed, L, cov, t0, nt, path, err=0.15) -> int:
     if n < 0:
         raise OSError(f"cannot write {path}")
     return n
+
+
+def backbone(seed, L, cov, t, err=0.15) -> bytes:
+    """The backbone target t's reads are drawn against (what gen_batch returns in Batch.backbones)."""
+    lib = _load()
+    p = _Params(seed, L, cov, err)
+    buf = C.create_string_buffer(L + 1)
+    lib.dgs_backbone(C.byref(p), t, buf)
+    return buf.raw[:L]
 
 
 def alns_per_target(cov):

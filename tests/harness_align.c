@@ -74,3 +74,38 @@ int64_t hal_align(const char* q, int64_t n, const char* t, int64_t m, int64_t ba
         return len;
     }
 }
+
+/* hal_lift: carries a read's alignment over from an OLD backbone to a NEW one through the alignment of the two
+ * backbones (iterative refinement, BASELINE configs[4]: the consensus of a round is the next round's backbone).
+ *   q, t, n        the read's gapped alignment to the old backbone, starting at old position s0 (0-based)
+ *   map_new[p]     index of the new base aligned to old base p, or -1 when old base p has no partner
+ *   next_new[p]    number of new bases in front of old position p (p = 0 .. old length)
+ *   nb             the new backbone
+ * Writes the gapped strings against the new backbone (capacity cap each), the 0-based new start and end, and
+ * returns their length (-1 when cap is too small).  Deterministic and O(n): both sides of the parity check are fed
+ * its output, and the bench excludes (and reports) its time. */
+int64_t hal_lift(const char* q, const char* t, int64_t n, int64_t s0, const int32_t* map_new, const int32_t* next_new,
+                 const char* nb, char* qo, char* to, int64_t cap, int64_t* new_start, int64_t* new_end) {
+    int64_t p = s0, j = next_new[s0], len = 0, c;
+    *new_start = j;
+    for (c = 0; c < n; c++) {
+        const char qc = q[c], tc = t[c];
+        if (len + 2 >= cap) return -1;
+        if (tc == '-') {
+            if (qc != '-') { qo[len] = qc; to[len] = '-'; len++; }
+            continue;
+        }
+        {
+            const int32_t tgt = map_new[p];
+            if (tgt >= 0) {
+                while (j < tgt) { if (len + 2 >= cap) return -1; qo[len] = '-'; to[len] = nb[j]; len++; j++; }
+                qo[len] = qc; to[len] = nb[j]; len++; j++;
+            } else if (qc != '-') {
+                qo[len] = qc; to[len] = '-'; len++;
+            }
+            p++;
+        }
+    }
+    *new_end = j;
+    return len;
+}
