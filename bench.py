@@ -44,7 +44,7 @@ MIN_COV, MIN_LEN, TRIM = 8, 500, 50
 CLI = os.path.join(ROOT, "pbdagcon_b200", "host", "pbdagcon")
 REF_CLI = os.path.join(ROOT, "oracle", "_ref", "pbdagcon_ref")
 
-SHAPES = {2: (8000, 30.0, 10000, 2), 4: (20000, 50.0, 2400, 4), 5: (40000, 100.0, 256, 5)}   # L, cov, targets/GPU, seed
+SHAPES = {2: (8000, 30.0, 10000, 2), 4: (20000, 50.0, 4800, 4), 5: (40000, 100.0, 256, 5)}   # L, cov, targets/GPU, seed
 
 
 def host_threads():
@@ -378,14 +378,18 @@ def bind_numa(dev):
     return info
 
 
-def pin_batches(api, subs):
+def pin_batches(api, subs, packed4=True):
+    """Page-locked staging buffers for the e2e arm.  packed4: the strings go to the device as 4-bit codes, two columns
+    per byte (DGC_BATCH_PACKED4) -- what the C++ packers of the CLI send; half the bytes on the link."""
+    import pbdagcon_b200.synth as synth
     pinned, sub_pb = [], []
     for b in subs:
-        pa = api.PinnedArray((b.arena.size,), np.uint8)
-        pa.array[:] = b.arena
-        b.arena = pa.array                      # drop the pageable copy
+        r = synth.pack4(b) if packed4 else None
+        arena, qo, to = r if r is not None else (b.arena, b.aln_q_off, b.aln_t_off)
+        pa = api.PinnedArray((arena.size,), np.uint8)
+        pa.array[:] = arena
         pinned.append(pa)
-        sub_pb.append(api.PackedBatch(b.tgt_tlen, b.tgt_aln_begin, b.aln_start, b.aln_len, b.aln_q_off, b.aln_t_off, pa.array))
+        sub_pb.append(api.PackedBatch(b.tgt_tlen, b.tgt_aln_begin, b.aln_start, b.aln_len, qo, to, pa.array, packed4=r is not None))
         assert sub_pb[-1].arena.ctypes.data == pa.ptr     # a view of the pinned array, not a copy
     return pinned, sub_pb
 
@@ -483,10 +487,15 @@ def run_gpu(args):
     rank_t0, rank_t1 = target_range(args.targets * WORLD, RANK, WORLD)
     subs = gen_workload(args.seed, args.L, args.cov, rank_t0, rank_t1 - rank_t0, args.sub, threads)
     import pbdagcon_b200.synth as synth
-    pinned, sub_pb = pin_batches(api, subs)
-    whole = api.PackedBatch.from_synth(synth.concat(subs)) if len(subs) > 1 else sub_pb[0]
+    pinned, sub_pb = pin_batches(api, subs, packed4=not args.ascii_wire)
+    if len(subs) > 1:
+        wb = synth.concat(subs)
+        whole = (None if args.ascii_wire else api.PackedBatch.from_synth_packed4(wb)) or api.PackedBatch.from_synth(wb)
+        del wb
+    else:
+        whole = sub_pb[0]
     gen_s = time.perf_counter() - t_gen
-    alg_in = whole.alg_bytes()
+    alg_in = sum(b.alg_bytes() for b in subs)
     h2d_bytes = sum(int(p.arena.size) + 4 * (2 * p.n_targets + 1) + 24 * p.n_alns + 8 * p.n_alns for p in sub_pb)
 
     eng = api.Consensus(min_cov=MIN_COV, min_len=MIN_LEN, trim=TRIM, device=dev, scratch_bytes=args.scratch_gb << 30, flags=args.flags)
@@ -594,7 +603,8 @@ def run_gpu(args):
             "warmup": args.warmup, "ms_per_step": dev_s * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
             "config": workload_config(args, sub_batch_targets=args.sub, targets_ok=n_ok, gen_seconds=round(gen_s, 1),
-                                      chunks_per_step=tm["chunks"], numa=numa),
+                                      chunks_per_step=tm["chunks"], numa=numa,
+                                      wire="ASCII" if args.ascii_wire else "4-bit codes (DGC_BATCH_PACKED4), packed on the host side of the C ABI"),
             "targets_per_s": tot_targets * args.steps / dev_s, "wall_ms_per_step": wall_s * 1e3 / args.steps,
             "e2e": {"value": e2e_val, "unit": "Mbp/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "targets_per_s": tot_targets * args.steps / e2e_s, "ms_per_step": e2e_s * 1e3 / args.steps},
@@ -623,9 +633,9 @@ def run_stream(args):
     passes = max(1, -(-share // pool))
     t_gen = time.perf_counter()
     subs = gen_workload(args.seed, args.L, args.cov, RANK * pool, pool, args.sub, threads)
-    pinned, sub_pb = pin_batches(api, subs)
+    pinned, sub_pb = pin_batches(api, subs, packed4=not args.ascii_wire)
     gen_s = time.perf_counter() - t_gen
-    alg_in = sum(p.alg_bytes() for p in sub_pb)
+    alg_in = sum(b.alg_bytes() for b in subs)
     h2d_bytes = sum(int(p.arena.size) + 4 * (2 * p.n_targets + 1) + 32 * p.n_alns for p in sub_pb)
     eng = api.Consensus(min_cov=MIN_COV, min_len=MIN_LEN, trim=TRIM, device=dev, scratch_bytes=args.scratch_gb << 30, flags=args.flags)
     _, _, kept = e2e_pass(api, eng, sub_pb, keep=True)         # warm-up pass, kept for parity
@@ -703,6 +713,7 @@ def main():
                     "submit: the library stages the upload itself)")
     ap.add_argument("--scratch-gb", type=int, default=0, help="dgc_opts.scratch_bytes in GiB (0 = the library default)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--ascii-wire", action="store_true", help="send the strings as ASCII (default: 4-bit codes, DGC_BATCH_PACKED4)")
     ap.add_argument("--cli-targets", type=int, default=2000, help="targets of the whole-process CLI comparison (0 = skip)")
     ap.add_argument("--cli-ref-reps", type=int, default=1)
     ap.add_argument("--flags", type=int, default=0, help="extra dgc_opts.flags (tuning, e.g. 256 = no prefetch)")
@@ -717,7 +728,8 @@ def main():
     args.targets = args.targets or nt
     args.seed = args.seed or seed
     if args.sub <= 0:
-        args.sub = args.targets
+        # config 4 streams: two sub-batches of half a pool in flight, so that the upload of one overlaps the kernels of the other
+        args.sub = args.targets // 2 if args.config == 4 else args.targets
     if args.config == 4 and args.targets_total <= 0:
         args.targets_total = 4 * args.targets * WORLD
     if args.impl == "reference":

@@ -62,6 +62,14 @@ typedef struct dgc_opts {
     uint64_t scratch_bytes; /* HBM budget for the per-chunk graph arena; 0 = default (112 GiB: 10 000 targets of 8 kb x 30x or 4 800 of 20 kb x 50x in one chunk) */
 } dgc_opts;
 
+/* dgc_batch.flags */
+#define DGC_BATCH_PACKED4 1u /* qstr/tstr travel as 4-bit codes, two columns per byte (column c of a string in byte c/2 of
+                                it, even columns in the low nibble): half the bytes on the PCIe link.  Codes index
+                                DGC_PACK4_ALPHABET; a string holding any other character cannot be packed (send that
+                                batch as ASCII).  Offsets and aln_len keep their meaning (byte offset of the string in the
+                                arena, number of columns); backbone strings (tgt_bb_off) stay ASCII. */
+#define DGC_PACK4_ALPHABET "-ACGTN."  /* codes 0..6 */
+
 /* Packed targets (SoA).  Host pointers; pinned memory (dgc_host_alloc) makes the H2D copy async.
  * Offsets are byte offsets into `arena`.  Strings need not be aligned or NUL-terminated. */
 typedef struct dgc_batch {
@@ -78,6 +86,8 @@ typedef struct dgc_batch {
     const uint64_t* aln_t_off;     /* [n_alns] */
     const uint8_t* arena;
     uint64_t arena_bytes;
+    uint32_t flags;                /* DGC_BATCH_* */
+    uint32_t reserved;
 } dgc_batch;
 
 /* Replaces std::vector<CnsResult> per target (src/cpp/AlnGraphBoost.hpp CnsResult; filled at

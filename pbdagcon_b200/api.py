@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libdagcon_b200.so")
 T_OK, T_SKIPPED, T_BAD_ALIGNMENT, T_TOO_MANY_ALNS, T_INTERNAL = 0, 1, 2, 3, 4
 F_NO_NORMALIZE, F_NO_TRIM, F_NO_MERGE, F_SINGLE = 1, 2, 4, 8
 MAX_INFLIGHT = 4
+BATCH_PACKED4 = 1
 
 EXPORTS = ["dgc_abi_version", "dgc_device_count", "dgc_create", "dgc_destroy", "dgc_last_error", "dgc_host_alloc",
            "dgc_host_free", "dgc_submit", "dgc_collect", "dgc_consensus", "dgc_upload", "dgc_run", "dgc_dbatch_free",
@@ -36,7 +37,7 @@ class CBatch(C.Structure):
     _fields_ = [("n_targets", C.c_uint32), ("n_alns", C.c_uint32),
                 ("tgt_tlen", C.c_void_p), ("tgt_aln_begin", C.c_void_p), ("tgt_bb_off", C.c_void_p),
                 ("aln_start", C.c_void_p), ("aln_len", C.c_void_p), ("aln_q_off", C.c_void_p), ("aln_t_off", C.c_void_p),
-                ("arena", C.c_void_p), ("arena_bytes", C.c_uint64)]
+                ("arena", C.c_void_p), ("arena_bytes", C.c_uint64), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class CResults(C.Structure):
@@ -127,7 +128,7 @@ def _ptr(a):
 class PackedBatch:
     """Holds the numpy arrays of a dgc_batch alive together with the C struct."""
 
-    def __init__(self, tgt_tlen, tgt_aln_begin, aln_start, aln_len, aln_q_off, aln_t_off, arena, tgt_bb_off=None, ids=None):
+    def __init__(self, tgt_tlen, tgt_aln_begin, aln_start, aln_len, aln_q_off, aln_t_off, arena, tgt_bb_off=None, ids=None, packed4=False):
         self.tgt_tlen = np.ascontiguousarray(tgt_tlen, np.uint32)
         self.tgt_aln_begin = np.ascontiguousarray(tgt_aln_begin, np.uint32)
         self.aln_start = np.ascontiguousarray(aln_start, np.uint32)
@@ -147,11 +148,29 @@ class PackedBatch:
         c.aln_start, c.aln_len = _ptr(self.aln_start), _ptr(self.aln_len)
         c.aln_q_off, c.aln_t_off = _ptr(self.aln_q_off), _ptr(self.aln_t_off)
         c.arena, c.arena_bytes = _ptr(self.arena), int(self.arena.size)
+        c.flags = BATCH_PACKED4 if packed4 else 0
+        self.packed4 = packed4
         self.c = c
 
     @classmethod
     def from_synth(cls, b, ids=None):
         return cls(b.tgt_tlen, b.tgt_aln_begin, b.aln_start, b.aln_len, b.aln_q_off, b.aln_t_off, b.arena, b.tgt_bb_off, ids)
+
+    @classmethod
+    def from_synth_packed4(cls, b, arena_out=None):
+        """The batch with its strings as 4-bit codes (DGC_BATCH_PACKED4): what a host packer sends to halve the bytes on
+        the link.  None when a string cannot be packed.  arena_out: optional preallocated (pinned) uint8 array factory
+        taking a size and returning an array to hold the packed arena."""
+        from . import synth
+        r = synth.pack4(b)
+        if r is None:
+            return None
+        arena, qo, to = r
+        if arena_out is not None:
+            dst = arena_out(arena.size)
+            dst[:] = arena
+            arena = dst
+        return cls(b.tgt_tlen, b.tgt_aln_begin, b.aln_start, b.aln_len, qo, to, arena, None, None, packed4=True)
 
     def alg_bytes(self):
         """Algorithmic input bytes: sum(2*len_raw + 16) per alignment + 16 per target (+ backbone)."""

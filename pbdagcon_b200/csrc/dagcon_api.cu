@@ -78,6 +78,7 @@ struct HostBuf {  // pinned
 struct dgc_dbatch {
     uint32_t T = 0, A = 0;
     bool has_bb = false;
+    bool packed4 = false;  // DGC_BATCH_PACKED4: the strings are 4-bit codes
     uint64_t arena_bytes = 0, norm_cols = 0, raw_cols = 0;
     DevBuf tgt_tlen, tgt_aln_begin, tgt_bb_off, aln_start, aln_len, aln_q_off, aln_t_off, aln_norm_off, arena;
     std::vector<uint32_t> h_tlen, h_aln_begin;  // host copies the planner needs
@@ -212,8 +213,9 @@ int validate_batch(const dgc_batch* b, std::string& err) {
             if (b->tgt_bb_off && (b->tgt_bb_off[t] > b->arena_bytes || b->tgt_tlen[t] > b->arena_bytes - b->tgt_bb_off[t])) { err = "backbone outside arena"; return DGC_E_INVALID; }
         }
     } else if (b->n_alns) { err = "alignments without targets"; return DGC_E_INVALID; }
+    if (b->flags & ~DGC_BATCH_PACKED4) { err = "unknown dgc_batch.flags"; return DGC_E_INVALID; }
     for (uint32_t k = 0; k < b->n_alns; k++) {
-        uint64_t n = b->aln_len[k];
+        uint64_t n = (b->flags & DGC_BATCH_PACKED4) ? ((uint64_t)b->aln_len[k] + 1) / 2 : b->aln_len[k];
         if (b->aln_q_off[k] > b->arena_bytes || n > b->arena_bytes - b->aln_q_off[k] || b->aln_t_off[k] > b->arena_bytes ||
             n > b->arena_bytes - b->aln_t_off[k]) {
             err = "alignment string outside arena"; return DGC_E_INVALID;
@@ -225,6 +227,7 @@ int validate_batch(const dgc_batch* b, std::string& err) {
 // H2D of a batch into db (async on s.stream; host arrays must stay valid until the stream syncs)
 int upload_batch(Slot& s, const dgc_batch* b, dgc_dbatch& db, bool timed, bool with_arena = true) {
     db.T = b->n_targets; db.A = b->n_alns; db.has_bb = b->tgt_bb_off != nullptr; db.arena_bytes = b->arena_bytes;
+    db.packed4 = (b->flags & DGC_BATCH_PACKED4) != 0;
     const size_t T = db.T, A = db.A;
     CU(db.tgt_tlen.ensure(4 * (T + 1))); CU(db.tgt_aln_begin.ensure(4 * (T + 1)));
     if (db.has_bb) CU(db.tgt_bb_off.ensure(8 * (T + 1)));
@@ -276,7 +279,7 @@ int launch_normalize(Slot& s, const dgc_dbatch& db, uint32_t k0, uint32_t k1) {
     NormArgs na;
     na.arena = db.arena.as<u8>(); na.aln_start = db.aln_start.as<u32>(); na.aln_len = db.aln_len.as<u32>();
     na.aln_q_off = db.aln_q_off.as<u64>(); na.aln_t_off = db.aln_t_off.as<u64>(); na.aln_norm_off = db.aln_norm_off.as<u64>();
-    na.n_alns = k1; na.aln_first = k0; na.min_len = o.min_len; na.trim = o.trim; na.flags = o.flags;
+    na.n_alns = k1; na.aln_first = k0; na.min_len = o.min_len; na.trim = o.trim; na.flags = (o.flags & 0xFFFFu) | (db.packed4 ? F_PACKED4 : 0u);
     na.norm = s.norm.as<u16>(); na.o_off = s.o_off.as<u64>(); na.o_len = s.o_len.as<u32>(); na.o_start = s.o_start.as<u32>();
     na.o_flags = s.o_flags.as<u32>(); na.o_nI = s.o_nI.as<u32>(); na.o_nE = s.o_nE.as<u32>(); na.o_tkept = s.o_tkept.as<u32>();
     const uint32_t n = k1 - k0;
@@ -706,7 +709,7 @@ bool split_pieces(const dgc_batch* b, uint32_t want, std::vector<Piece>& out) {
         uint64_t lo = ~0ull, h = 0;
         if (b->tgt_bb_off) { lo = b->tgt_bb_off[t]; h = lo + b->tgt_tlen[t]; }
         for (uint32_t k = b->tgt_aln_begin[t]; k < b->tgt_aln_begin[t + 1]; k++) {
-            const uint64_t n = b->aln_len[k], q = b->aln_q_off[k], tt = b->aln_t_off[k];
+            const uint64_t n = (b->flags & DGC_BATCH_PACKED4) ? ((uint64_t)b->aln_len[k] + 1) / 2 : b->aln_len[k], q = b->aln_q_off[k], tt = b->aln_t_off[k];
             lo = std::min(lo, std::min(q, tt));
             h = std::max(h, std::max(q, tt) + n);
         }
@@ -1093,7 +1096,7 @@ int build_daz_batch(Slot& s, const dgc_daz_batch* b, bool strings_only) {
     }
     p_segb[O] = nseg_tot;
     if (arena > (1ull << 40) || nseg_tot > 0x7FFFFFF0u) { s.err = "dazcon batch too large"; return DGC_E_NOMEM; }
-    db.T = (uint32_t)T; db.A = (uint32_t)O; db.has_bb = true; db.arena_bytes = arena; db.norm_cols = norm; db.raw_cols = raw;
+    db.T = (uint32_t)T; db.A = (uint32_t)O; db.has_bb = true; db.packed4 = false; db.arena_bytes = arena; db.norm_cols = norm; db.raw_cols = raw;
     db.h_tlen.assign(p_tlen, p_tlen + T);
     db.h_aln_begin.assign(b->tgt_ovl_begin, b->tgt_ovl_begin + T + 1);
     if (T == 0) return DGC_OK;

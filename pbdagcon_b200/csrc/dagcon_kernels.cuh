@@ -36,6 +36,14 @@ typedef unsigned long long u64;
 #define F_NO_MERGE 4u
 #define F_SINGLE 8u
 #define F_NO_PREFETCH 256u
+#define F_PACKED4 0x10000u  // internal (NormArgs.flags): the batch's strings are 4-bit codes (DGC_BATCH_PACKED4)
+
+// 4-bit wire codes -> ASCII: "-ACGTN." (code 7 is never sent; it reads as 'N')
+#define PACK4_LUT_LO 0x4743412Du   // codes 0..3: '-' 'A' 'C' 'G' (little-endian bytes)
+#define PACK4_LUT_HI 0x4E2E4E54u   // codes 4..7: 'T' 'N' '.' 'N'
+__device__ __forceinline__ u32 pack4_ascii(u32 code) {
+    return ((code & 4u ? PACK4_LUT_HI : PACK4_LUT_LO) >> (8u * (code & 3u))) & 0xFFu;
+}
 
 __device__ __forceinline__ u32 n_base(u32 bfv) { return bfv & 0xFFu; }
 __device__ __forceinline__ u32 n_flags(u32 bfv) { return (bfv >> 8) & 0xFFu; }
@@ -53,19 +61,22 @@ __device__ __forceinline__ u32 n_vis(u32 bfv) { return bfv >> 16; }
 struct ByteStream {
     const u64* w;
     u64 off, ci, cw;
-    __device__ __forceinline__ void init(const u8* base, u64 o) {
+    u32 packed;   // the string is 4-bit codes, two columns per byte (DGC_BATCH_PACKED4)
+    __device__ __forceinline__ void init(const u8* base, u64 o, u32 packed4 = 0) {
         w = (const u64*)base;
         off = o;
         ci = ~0ull;
         cw = 0;
+        packed = packed4;
     }
     __device__ __forceinline__ u32 get(u64 r) {
-        u64 a = off + r, wi = a >> 3;
+        u64 a = off + (packed ? r >> 1 : r), wi = a >> 3;
         if (wi != ci) {
             cw = __ldg(w + wi);
             ci = wi;
         }
-        return (u32)(cw >> ((a & 7u) * 8u)) & 0xFFu;
+        const u32 b = (u32)(cw >> ((a & 7u) * 8u)) & 0xFFu;
+        return packed ? pack4_ascii((b >> (4u * (u32)(r & 1u))) & 7u) : b;
     }
 };
 
@@ -133,8 +144,8 @@ __global__ void __launch_bounds__(128) k_normalize_trim(NormArgs a) {
         return;
     }
     ByteStream mq, mt;
-    mq.init(a.arena, a.aln_q_off[ai]);
-    mt.init(a.arena, a.aln_t_off[ai]);
+    mq.init(a.arena, a.aln_q_off[ai], a.flags & F_PACKED4);
+    mt.init(a.arena, a.aln_t_off[ai], a.flags & F_PACKED4);
     if (a.flags & F_NO_NORMALIZE) {
         for (u64 r = 0; r < n; r++) out[m++] = (u16)(mq.get(r) | (mt.get(r) << 8));
     } else {

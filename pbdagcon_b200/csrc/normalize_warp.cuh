@@ -118,6 +118,23 @@ __device__ __forceinline__ void nw_stage(const u8* src, u32 nbytes, u32* dst, u3
     }
 }
 
+// the same for a string sent as 4-bit codes (DGC_BATCH_PACKED4): `src` = the byte holding the window's first column (the
+// windows start on even columns), `ncols` columns.  One prmt turns four codes into four ASCII bytes.
+__device__ __forceinline__ void nw_stage_packed(const u8* src, u32 ncols, u32* dst, u32 lane) {
+    const unsigned long long a = (unsigned long long)src;
+    const u32 ph = (u32)(a & 3ull);
+    const u32* w = (const u32*)(a - ph);
+    const u32 nw = (((ncols + 1) >> 1) + 3) >> 2;   // packed words: 8 columns each
+    for (u32 i = lane; i < nw; i += 32) {
+        const u32 lo = __ldg(w + i), hi = ph ? __ldg(w + i + 1) : 0u;
+        const u32 x = __funnelshift_r(lo, hi, 8 * ph);
+        uint2 o;
+        o.x = __byte_perm(PACK4_LUT_LO, PACK4_LUT_HI, x & 0x7777u);
+        o.y = __byte_perm(PACK4_LUT_LO, PACK4_LUT_HI, (x >> 16) & 0x7777u);
+        ((uint2*)dst)[i] = o;
+    }
+}
+
 __device__ __forceinline__ u32 warp_incl_scan(u32 v, u32 lane) {
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -152,8 +169,13 @@ __global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp
         const u32 nwin = min(NW_W, n - c0);
         const u32 more = c0 + NW_W < n ? 1u : 0u;
         __syncwarp();
-        nw_stage(qsrc + c0, nwin, (u32*)sm.q, lane);
-        nw_stage(tsrc + c0, nwin, (u32*)sm.t, lane);
+        if (a.flags & F_PACKED4) {
+            nw_stage_packed(qsrc + (c0 >> 1), nwin, (u32*)sm.q, lane);
+            nw_stage_packed(tsrc + (c0 >> 1), nwin, (u32*)sm.t, lane);
+        } else {
+            nw_stage(qsrc + c0, nwin, (u32*)sm.q, lane);
+            nw_stage(tsrc + c0, nwin, (u32*)sm.t, lane);
+        }
         __syncwarp();
         // ---- the lane's 32 tile columns and 8 margin columns in registers
         u32 qw[8], tw[8], qm[2], tm[2];

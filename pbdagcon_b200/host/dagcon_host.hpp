@@ -134,6 +134,11 @@ public:
     uint32_t n_targets = 0, n_alns = 0;
     uint64_t arena_bytes = 0;
     bool has_backbone = false;
+    // The strings are stored as 4-bit codes, two columns per byte (DGC_BATCH_PACKED4): half the bytes to page-lock and to
+    // send.  Set before the first add_*; an add_* that meets a character outside DGC_PACK4_ALPHABET throws NeedAscii
+    // and the caller packs the unit again with packed4 = false.
+    bool packed4 = false;
+    struct NeedAscii {};
     std::vector<std::string> ids;   // Alignment::id of alns[0] per target
     uint64_t seq = 0;               // position in the input stream (batch number)
     std::unique_ptr<DazPayload> daz;   // set: submit with dgc_submit_daz (n_targets and ids are filled, the arrays below unused)
@@ -180,6 +185,7 @@ struct ProgramOpts {
     size_t batchTargets = 256;          // a batch closes at this many targets or this much input text: small enough
     size_t batchBytes = 192ull << 20;   // that several are being packed at once and the page-locked ring stays small
     bool stats = false;
+    bool asciiWire = false;             // --ascii-wire: send the alignment strings as ASCII instead of 4-bit codes
 };
 
 struct RunStats {

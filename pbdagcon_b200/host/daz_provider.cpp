@@ -555,6 +555,7 @@ struct DazFront {
                         hb->clear();
                         hb->seq = u->seq;
                         hb->daz.reset();
+                        hb->packed4 = !opts.asciiWire && pinned;   // host-rebuilt strings are over "ACGT-.": always packable
                         if (unit_device_ok(*u)) {
                             pack_device(*u, *hb);
                             u.reset();
@@ -563,7 +564,7 @@ struct DazFront {
                         }
                         size_t nal = 0, bb = 0;
                         for (auto& p : u->piles) { nal += p.recs.size(); bb += (size_t)p.length + 16; }
-                        hb->reserve(2 * (u->cols + u->cols / 6) + 64 * nal + bb, nal, u->piles.size());
+                        hb->reserve((hb->packed4 ? 1 : 2) * (u->cols + u->cols / 6) + 64 * nal + bb, nal, u->piles.size());
                         need_rz();
                         if (rz) for (auto& p : u->piles) {
                             alns.resize(p.recs.size());

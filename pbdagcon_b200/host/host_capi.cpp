@@ -50,6 +50,7 @@ void* dgh_pack_file(const char* path, int fmt, uint32_t min_cov, int threads, ui
     Packed* p = new Packed();
     dgh::ProgramOpts o;
     o.input = path; o.minCov = min_cov; o.threads = threads; o.align = fmt == 1;
+    o.asciiWire = true;   // the tests read the packed strings back as text
     if (batch_targets) o.batchTargets = batch_targets;
     if (batch_bytes) o.batchBytes = batch_bytes;
     const int rc = dgh::pack_text(o, false, sink, p, p->st, p->err);

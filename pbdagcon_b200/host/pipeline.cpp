@@ -202,8 +202,9 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
     std::string err;
     int rc = 0;
     int live_packers = 0;
+    bool wire4 = true;   // 4-bit wire format (ProgramOpts::asciiWire switches it off)
 
-    Front(const ProgramOpts& o_, bool pinned_, RunStats& st_) : o(o_), fmt(o_.align ? TextFormat::PRE : TextFormat::M5), pinned(pinned_), st(st_) {}
+    Front(const ProgramOpts& o_, bool pinned_, RunStats& st_) : o(o_), fmt(o_.align ? TextFormat::PRE : TextFormat::M5), pinned(pinned_), st(st_) { wire4 = !o_.asciiWire; }
 
     void fail(int code, const std::string& msg) {
         std::lock_guard<std::mutex> lk(err_mu);
@@ -281,18 +282,28 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); break; }
                     if (!units.pop(u)) { free_batches.push(std::move(hb)); break; }  // hand the batch on: another packer may be waiting for one just to find the input exhausted
                     try {
-                        hb->clear();
-                        hb->seq = u->seq;
-                        // m5 lines carry the two strings plus a match pattern of the same length; aligned 'pre'
-                        // strings grow by their gaps (a low guess only costs one doubling)
-                        hb->reserve((fmt == TextFormat::M5 ? u->bytes * 2 / 3 : u->bytes + u->bytes / 4) + 64 * u->lines.size(),
-                                    u->lines.size(), u->targets());
                         std::vector<PreAligned> aligned;
                         if (fmt == TextFormat::PRE) align_unit(*u, aligned);
                         std::vector<std::pair<const char*, size_t>> lines;
-                        for (size_t t = 0; t + 1 < u->tgt_begin.size(); t++) {
-                            lines.assign(u->lines.begin() + u->tgt_begin[t], u->lines.begin() + u->tgt_begin[t + 1]);
-                            hb->add_target_lines(lines, fmt, aligned.empty() ? nullptr : &aligned[u->tgt_begin[t]]);
+                        // the strings go out as 4-bit codes (half the bytes to page-lock and to send); a unit with a
+                        // character outside "-ACGTN." is packed again as ASCII
+                        for (int pass = wire4 ? 0 : 1; pass < 2; pass++) {
+                            hb->clear();
+                            hb->seq = u->seq;
+                            hb->packed4 = pass == 0;
+                            // m5 lines carry the two strings plus a match pattern of the same length; aligned 'pre'
+                            // strings grow by their gaps (a low guess only costs one doubling)
+                            const size_t est = fmt == TextFormat::M5 ? u->bytes * 2 / 3 : u->bytes + u->bytes / 4;
+                            hb->reserve((hb->packed4 ? est / 2 : est) + 64 * u->lines.size(), u->lines.size(), u->targets());
+                            try {
+                                for (size_t t = 0; t + 1 < u->tgt_begin.size(); t++) {
+                                    lines.assign(u->lines.begin() + u->tgt_begin[t], u->lines.begin() + u->tgt_begin[t + 1]);
+                                    hb->add_target_lines(lines, fmt, aligned.empty() ? nullptr : &aligned[u->tgt_begin[t]]);
+                                }
+                                break;
+                            } catch (const HostBatch::NeedAscii&) {
+                                if (pass == 1) throw M5Exception::FormatError{"unpackable character in an ASCII batch"};
+                            }
                         }
                     } catch (const M5Exception::FormatError& e) { fail(DGC_E_INVALID, "Format error. Input: " + o.input + ", Error: " + e.msg);
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); }

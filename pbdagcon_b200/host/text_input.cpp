@@ -193,6 +193,47 @@ void HostBatch::need_targets(size_t extra) {
 
 static inline uint64_t align16(uint64_t x) { return (x + 15) & ~15ull; }
 
+// ---- 4-bit wire codes (include/dagcon_b200.h: DGC_PACK4_ALPHABET "-ACGTN.")
+namespace {
+struct Pack4Tables {
+    uint8_t code[256], rc[256];   // code of a character / of its complement as revComp forms it (Alignment.cpp:15-26)
+    Pack4Tables() {
+        memset(code, 0xFF, sizeof code);
+        const char* al = DGC_PACK4_ALPHABET;
+        for (int i = 0; al[i]; i++) code[(uint8_t)al[i]] = (uint8_t)i;
+        memcpy(rc, code, sizeof rc);
+        rc[(uint8_t)'A'] = code[(uint8_t)'T']; rc[(uint8_t)'T'] = code[(uint8_t)'A'];
+        rc[(uint8_t)'C'] = code[(uint8_t)'G']; rc[(uint8_t)'G'] = code[(uint8_t)'C'];
+    }
+};
+const Pack4Tables kP4;
+
+// columns src[0..n) -> n/2 (rounded up) bytes at dst, even columns in the low nibble; false on a foreign character
+inline bool pack4_into(const char* src, size_t n, uint8_t* dst) {
+    uint8_t bad = 0;
+    size_t c = 0;
+    for (; c + 1 < n; c += 2) {
+        const uint8_t a = kP4.code[(uint8_t)src[c]], b = kP4.code[(uint8_t)src[c + 1]];
+        bad |= a | b;
+        dst[c >> 1] = (uint8_t)(a | (b << 4));
+    }
+    if (c < n) { const uint8_t a = kP4.code[(uint8_t)src[c]]; bad |= a; dst[c >> 1] = a; }
+    return !(bad & 0x80);
+}
+// the same for the reverse complement of src (revcomp_into followed by pack4_into, in one pass)
+inline bool pack4_revcomp_into(const char* src, size_t n, uint8_t* dst) {
+    uint8_t bad = 0;
+    size_t c = 0;
+    for (; c + 1 < n; c += 2) {
+        const uint8_t a = kP4.rc[(uint8_t)src[n - 1 - c]], b = kP4.rc[(uint8_t)src[n - 2 - c]];
+        bad |= a | b;
+        dst[c >> 1] = (uint8_t)(a | (b << 4));
+    }
+    if (c < n) { const uint8_t a = kP4.rc[(uint8_t)src[n - 1 - c]]; bad |= a; dst[c >> 1] = a; }
+    return !(bad & 0x80);
+}
+}  // namespace
+
 // One 'pre' line through the -a step: ungapped segments in, gapped strings in target orientation out
 // (reference main.cpp:127-129 -> SimpleAligner.cpp:25-63).
 bool align_pre_line(const char* p, size_t n, PreAligned& out) {
@@ -249,17 +290,22 @@ void HostBatch::add_target_lines(const std::vector<std::pair<const char*, size_t
             ids.emplace_back(f.id, f.id_len);
             first = false;
         }
-        const size_t n = f.q_len;
-        need_arena(2 * (n + 16));
-        const uint64_t qo = align16(arena_bytes), to = align16(qo + n);
-        if (fmt == TextFormat::M5 && f.strand == '-') {  // Alignment.cpp:72-76
+        const size_t n = f.q_len, nb = packed4 ? (n + 1) / 2 : n;
+        need_arena(2 * (nb + 16));
+        const uint64_t qo = align16(arena_bytes), to = align16(qo + nb);
+        const bool rc = fmt == TextFormat::M5 && f.strand == '-';  // Alignment.cpp:72-76
+        if (packed4) {
+            const bool ok = rc ? (pack4_revcomp_into(f.q, n, arena + qo) && pack4_revcomp_into(f.t, n, arena + to))
+                               : (pack4_into(f.q, n, arena + qo) && pack4_into(f.t, n, arena + to));
+            if (!ok) throw NeedAscii{};
+        } else if (rc) {
             revcomp_into(f.q, n, arena + qo);
             revcomp_into(f.t, n, arena + to);
         } else {
             memcpy(arena + qo, f.q, n);
             memcpy(arena + to, f.t, n);
         }
-        arena_bytes = to + n;
+        arena_bytes = to + nb;
         aln_start[n_alns] = f.start;
         aln_len[n_alns] = (uint32_t)n;
         aln_q_off[n_alns] = qo;
@@ -293,12 +339,16 @@ void HostBatch::add_target(const std::vector<dagcon::Alignment>& alns, const std
     }
     for (const auto& a : alns) {
         if (a.qstr.size() != a.tstr.size()) throw M5Exception::FormatError{"query and target alignment strings differ in length"};
-        const size_t n = a.qstr.size();
-        need_arena(2 * (n + 16));
-        const uint64_t qo = align16(arena_bytes), to = align16(qo + n);
-        memcpy(arena + qo, a.qstr.data(), n);
-        memcpy(arena + to, a.tstr.data(), n);
-        arena_bytes = to + n;
+        const size_t n = a.qstr.size(), nb = packed4 ? (n + 1) / 2 : n;
+        need_arena(2 * (nb + 16));
+        const uint64_t qo = align16(arena_bytes), to = align16(qo + nb);
+        if (packed4) {
+            if (!pack4_into(a.qstr.data(), n, arena + qo) || !pack4_into(a.tstr.data(), n, arena + to)) throw NeedAscii{};
+        } else {
+            memcpy(arena + qo, a.qstr.data(), n);
+            memcpy(arena + to, a.tstr.data(), n);
+        }
+        arena_bytes = to + nb;
         aln_start[n_alns] = a.start;
         aln_len[n_alns] = (uint32_t)n;
         aln_q_off[n_alns] = qo;
@@ -322,6 +372,8 @@ dgc_batch HostBatch::view() const {
     b.aln_t_off = aln_t_off;
     b.arena = arena;
     b.arena_bytes = arena_bytes;
+    b.flags = packed4 ? DGC_BATCH_PACKED4 : 0u;
+    b.reserved = 0;
     return b;
 }
 

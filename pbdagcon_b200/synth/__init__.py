@@ -40,6 +40,8 @@ def _load():
         _lib.dgs_write_m5.argtypes = [C.POINTER(_Params), C.c_uint64, C.c_uint32, C.c_char_p]
         _lib.dgs_alns_per_target.argtypes = [C.POINTER(_Params)]
         _lib.dgs_backbone.argtypes = [C.POINTER(_Params), C.c_uint64, C.c_char_p]
+        _lib.dgs_pack4.restype = C.c_int64
+        _lib.dgs_pack4.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     return _lib
 
 
@@ -119,6 +121,24 @@ def backbone(seed, L, cov, t, err=0.15) -> bytes:
     buf = C.create_string_buffer(L + 1)
     lib.dgs_backbone(C.byref(p), t, buf)
     return buf.raw[:L]
+
+
+def pack4(b: Batch):
+    """(arena, aln_q_off, aln_t_off) of the batch with its strings as 4-bit codes, two columns per byte
+    (DGC_BATCH_PACKED4), or None when a string holds a character outside "-ACGTN."; batches with backbone strings are
+    not handled here."""
+    lib = _load()
+    assert b.tgt_bb_off is None
+    ln = np.ascontiguousarray(b.aln_len, np.uint32)
+    cap = int((((ln.astype(np.int64) + 1) // 2 + 15) & ~15).sum()) * 2 + 16
+    out = np.zeros(cap, np.uint8)
+    qo, to = np.zeros(b.n_alns, np.uint64), np.zeros(b.n_alns, np.uint64)
+    arena = np.ascontiguousarray(b.arena, np.uint8)
+    n = lib.dgs_pack4(arena.ctypes.data, b.n_alns, ln.ctypes.data, np.ascontiguousarray(b.aln_q_off, np.uint64).ctypes.data,
+                      np.ascontiguousarray(b.aln_t_off, np.uint64).ctypes.data, out.ctypes.data, qo.ctypes.data, to.ctypes.data)
+    if n < 0:
+        return None
+    return out[:n], qo, to
 
 
 def alns_per_target(cov):

@@ -194,3 +194,34 @@ int64_t dgs_write_m5(const dgs_params* p, uint64_t t0, uint32_t nt, const char* 
     fclose(f);
     return total;
 }
+
+/* The strings of a batch as 4-bit codes, two columns per byte (include/dagcon_b200.h: DGC_BATCH_PACKED4): what a packer
+ * on the host side of the C ABI does before the upload.  out needs sum(16 + (len+1)/2 rounded up to 16) * 2 bytes.
+ * Returns the packed arena's size, or -1 when a string holds a character outside "-ACGTN.". */
+int64_t dgs_pack4(const uint8_t* arena, uint32_t n_alns, const uint32_t* len, const uint64_t* qoff, const uint64_t* toff,
+                  uint8_t* out, uint64_t* new_qoff, uint64_t* new_toff) {
+    uint8_t code[256];
+    uint64_t pos = 0;
+    uint32_t k;
+    memset(code, 0xFF, sizeof code);
+    code['-'] = 0; code['A'] = 1; code['C'] = 2; code['G'] = 3; code['T'] = 4; code['N'] = 5; code['.'] = 6;
+    for (k = 0; k < n_alns; k++) {
+        int s;
+        for (s = 0; s < 2; s++) {
+            const uint8_t* src = arena + (s ? toff[k] : qoff[k]);
+            const uint32_t n = len[k];
+            uint32_t c;
+            uint8_t bad = 0;
+            if (s) new_toff[k] = pos; else new_qoff[k] = pos;
+            for (c = 0; c + 1 < n; c += 2) {
+                const uint8_t a = code[src[c]], b = code[src[c + 1]];
+                bad |= a | b;
+                out[pos + (c >> 1)] = (uint8_t)(a | (b << 4));
+            }
+            if (c < n) { const uint8_t a = code[src[c]]; bad |= a; out[pos + (c >> 1)] = a; }
+            if (bad & 0x80) return -1;
+            pos += (((uint64_t)n + 1) / 2 + 15) & ~15ull;
+        }
+    }
+    return (int64_t)pos;
+}

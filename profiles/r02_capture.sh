@@ -30,7 +30,7 @@ for s in $STEPS; do
 import time, pbdagcon_b200.synth as s
 t=time.time(); n=s.write_m5(2,8000,30,0,10000,"/dev/shm/c2_10k.m5"); print("m5 bytes",n,"gen s",round(time.time()-t,1))
 PY
-      for j in 16 32; do /usr/bin/time -f "wall %e s" pbdagcon_b200/host/pbdagcon -c 8 -j $j --stats /dev/shm/c2_10k.m5 > /dev/shm/out_gpu.fa 2> gpurun_out/${TAG}_cli10k_j$j.err; tail -2 gpurun_out/${TAG}_cli10k_j$j.err; done
+      for j in 16 32; do for bt in 256 1024; do t0=$(date +%s.%N); pbdagcon_b200/host/pbdagcon -c 8 -j $j --batch-targets $bt --batch-mb $((bt*3/4)) --stats /dev/shm/c2_10k.m5 > /dev/shm/out_gpu.fa 2> gpurun_out/${TAG}_cli10k_j${j}_b$bt.err; t1=$(date +%s.%N); echo "j=$j batch-targets=$bt wall $(echo "$t1 - $t0" | bc) s"; tail -1 gpurun_out/${TAG}_cli10k_j${j}_b$bt.err; done; done
       rm -f /dev/shm/c2_10k.m5 /dev/shm/out_gpu.fa ;;
   esac
 done

@@ -33,7 +33,7 @@ def test_exports_match_header(lib_path):
 def test_struct_layouts_match_header():
     import pbdagcon_b200.api as api
     assert C.sizeof(api.Opts) == 32
-    assert C.sizeof(api.CBatch) == 8 + 8 * 8 + 8
+    assert C.sizeof(api.CBatch) == 8 + 8 * 8 + 8 + 8
     assert C.sizeof(api.CResults) == 8 + 8 * 7 + 8
     assert C.sizeof(api.Timings) == 10 * 4 + 2 * 4 + 4 * 8 + 2 * 4
 

@@ -221,3 +221,26 @@ def test_cli_align_first_on_pre_records(api, tmp_path):
                          text=True, timeout=300)
     assert ref.returncode == 0
     assert canon(out) == canon(ref.stdout)
+
+
+def test_cli_wire_formats_print_the_same_fasta(api, tmp_path):
+    """The packers send 4-bit codes by default; --ascii-wire and an input with characters outside "-ACGTN." (which falls
+    back to ASCII batch by batch) must print the same bytes."""
+    import pbdagcon_b200.synth as synth
+    path = str(tmp_path / "w.m5")
+    synth.write_m5(13, 2500, 16, 0, 60, path)
+    a = run_cli(["-c", "6", "-m", "200", "-j", "3", "--batch-targets", "8"], path)
+    b = run_cli(["-c", "6", "-m", "200", "-j", "3", "--batch-targets", "8", "--ascii-wire"], path)
+    assert a == b and a.count(">") >= 60
+    # lower-case a base in ONE record of the 20th target: its batch goes out as ASCII, the others packed
+    lines = open(path).read().split("\n")
+    tgt = lines[0].split(" ")[5]
+    k = next(i for i, ln in enumerate(lines) if ln and ln.split(" ")[5] != tgt and i > 19 * 20)
+    f = lines[k].split(" ")
+    f[16] = f[16][:50] + f[16][50:60].lower() + f[16][60:]
+    lines[k] = " ".join(f)
+    p2 = str(tmp_path / "w2.m5")
+    open(p2, "w").write("\n".join(lines))
+    c = run_cli(["-c", "6", "-m", "200", "-j", "3", "--batch-targets", "8"], p2)
+    d = run_cli(["-c", "6", "-m", "200", "-j", "3", "--batch-targets", "8", "--ascii-wire"], p2)
+    assert c == d and c.count(">") >= 59

@@ -463,3 +463,49 @@ def test_staged_output_buffers_grow_across_chunks(api, synth, monkeypatch):
             assert list(r.status) == want_status
             assert [r.frags(t) for t in range(r.n_targets)] == want, (scratch, rep)
         eng.close()
+
+
+def test_packed4_wire_format_equals_ascii(api, synth):
+    """DGC_BATCH_PACKED4: the strings as 4-bit codes, two columns per byte.  Same normalised strings and the same
+    consensus as the ASCII batch, on fuzzed targets with '.', 'N', odd lengths and strings at every byte phase; through
+    the warp normaliser, the serial one (F_NO_NORMALIZE) and the staged upload."""
+    targets = _fuzz_targets(901, 120) + [(L, bb, alns) for L, bb, alns in _fuzz_targets(902, 40, min_span=5) if alns]
+    sb = synth.from_python(targets)
+    asc = api.PackedBatch.from_synth(sb)
+    pk = api.PackedBatch.from_synth_packed4(sb)
+    assert pk is not None and pk.packed4 and pk.arena.size < 0.6 * asc.arena.size
+    # the same packed strings at byte phases 1..3 (the device realigns to words itself)
+    shifted = []
+    for ph in (1, 2, 3):
+        arena = np.concatenate([np.zeros(ph, np.uint8), pk.arena])
+        shifted.append(api.PackedBatch(pk.tgt_tlen, pk.tgt_aln_begin, pk.aln_start, pk.aln_len, pk.aln_q_off + np.uint64(ph),
+                                       pk.aln_t_off + np.uint64(ph), arena, packed4=True))
+    for flags in (0, api.F_NO_NORMALIZE):
+        eng = api.Consensus(min_cov=2, min_len=10, trim=3, flags=flags)
+        want_norm = eng.debug_normalize(asc)
+        want = eng(asc)
+        for b in [pk] + shifted:
+            assert eng.debug_normalize(b) == want_norm
+            got = eng(b)
+            assert list(got.status) == list(want.status)
+            assert [got.frags(t) for t in range(got.n_targets)] == [want.frags(t) for t in range(want.n_targets)]
+        eng.close()
+    # a character outside "-ACGTN." cannot be packed: the packer says so (and sends ASCII)
+    assert api.PackedBatch.from_synth_packed4(synth.from_python([(10, None, [(b"ACgT", b"ACGT", 1)])])) is None
+
+
+def test_packed4_large_alignments_and_staged_upload(api, synth, monkeypatch):
+    sb = synth.gen_batch(seed=61, L=6000, cov=14, t0=0, nt=40)      # several 1024-column tiles per alignment, look-ahead margins
+    asc, pk = api.PackedBatch.from_synth(sb), api.PackedBatch.from_synth_packed4(sb)
+    eng = api.Consensus(min_cov=4, min_len=200, trim=20)
+    want = eng(asc)
+    wf = [want.frags(t) for t in range(want.n_targets)]
+    assert [eng(pk).frags(t) for t in range(want.n_targets)] == wf
+    eng.close()
+    monkeypatch.setenv("DGC_STAGE_MIN_BYTES", "1")
+    monkeypatch.setenv("DGC_STAGE_PIECE_BYTES", str(1 << 18))
+    eng = api.Consensus(min_cov=4, min_len=200, trim=20, scratch_bytes=64 << 20)
+    eng.submit(pk)
+    r = eng.collect()
+    assert eng.timings()["chunks"] >= 2 and [r.frags(t) for t in range(r.n_targets)] == wf
+    eng.close()
