@@ -728,8 +728,7 @@ def main():
     args.targets = args.targets or nt
     args.seed = args.seed or seed
     if args.sub <= 0:
-        # config 4 streams: two sub-batches of half a pool in flight, so that the upload of one overlaps the kernels of the other
-        args.sub = args.targets // 2 if args.config == 4 else args.targets
+        args.sub = args.targets
     if args.config == 4 and args.targets_total <= 0:
         args.targets_total = 4 * args.targets * WORLD
     if args.impl == "reference":

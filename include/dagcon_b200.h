@@ -185,6 +185,30 @@ int dgc_submit_daz(dgc_handle* h, const dgc_daz_batch* batch);
 int dgc_debug_daz_strings(dgc_handle* h, const dgc_daz_batch* batch, uint8_t* out_q, uint8_t* out_t, uint64_t out_cap,
                           uint64_t* out_off, uint32_t* out_len);
 
+/* ---- `pbdagcon -a`: ungapped 'pre' records in, consensus out (the alignment step runs on the device) ---------------
+ * Replaces `std::for_each(alns.begin(), alns.end(), SimpleAligner())` (src/cpp/main.cpp:127-129) and
+ * SimpleAligner::align (src/cpp/SimpleAligner.cpp:25-63) in front of the consensus path.  The reference's arithmetic
+ * there is blasr_libcpp's (source absent): this aligner is the repository's own banded DP; the
+ * coordinate and strand bookkeeping of SimpleAligner.cpp:49-62 is the reference's. */
+typedef struct dgc_pre_batch {
+    uint32_t n_targets;
+    uint32_t n_recs;
+    const uint32_t* tgt_tlen;       /* [n_targets] */
+    const uint32_t* tgt_rec_begin;  /* [n_targets+1] CSR into the record arrays */
+    const uint32_t* rec_start;      /* [n_recs] tstart of the 'pre' line (0-based, on the record's strand; Alignment.cpp:95-111) */
+    const uint32_t* rec_strand;     /* [n_recs] 0 = '+', 1 = '-' */
+    const uint32_t* rec_qlen;       /* [n_recs] ungapped query segment length */
+    const uint32_t* rec_tseglen;    /* [n_recs] ungapped target segment length */
+    const uint64_t* rec_q_off;      /* [n_recs] into arena (ASCII) */
+    const uint64_t* rec_t_off;
+    const uint8_t* arena;
+    uint64_t arena_bytes;
+} dgc_pre_batch;
+int dgc_submit_pre(dgc_handle* h, const dgc_pre_batch* batch);
+/* Test hook: the gapped strings and Alignment::start the device produced for every record (0 columns = nothing aligns). */
+int dgc_debug_pre_strings(dgc_handle* h, const dgc_pre_batch* batch, uint8_t* out_q, uint8_t* out_t, uint64_t out_cap,
+                          uint64_t* out_off, uint32_t* out_len, uint32_t* out_start);
+
 /* Synchronous convenience: submit + collect. */
 int dgc_consensus(dgc_handle* h, const dgc_batch* batch, dgc_results* out);
 

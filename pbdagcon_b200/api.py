@@ -21,7 +21,7 @@ BATCH_PACKED4 = 1
 EXPORTS = ["dgc_abi_version", "dgc_device_count", "dgc_create", "dgc_destroy", "dgc_last_error", "dgc_host_alloc",
            "dgc_host_free", "dgc_submit", "dgc_collect", "dgc_consensus", "dgc_upload", "dgc_run", "dgc_dbatch_free",
            "dgc_get_timings", "dgc_debug_normalize", "dgc_debug_graph", "dgc_debug_free",
-           "dgc_daz_set_db", "dgc_submit_daz", "dgc_debug_daz_strings"]
+           "dgc_daz_set_db", "dgc_submit_daz", "dgc_debug_daz_strings", "dgc_submit_pre", "dgc_debug_pre_strings"]
 
 
 class DagconError(RuntimeError):
@@ -38,6 +38,38 @@ class CBatch(C.Structure):
                 ("tgt_tlen", C.c_void_p), ("tgt_aln_begin", C.c_void_p), ("tgt_bb_off", C.c_void_p),
                 ("aln_start", C.c_void_p), ("aln_len", C.c_void_p), ("aln_q_off", C.c_void_p), ("aln_t_off", C.c_void_p),
                 ("arena", C.c_void_p), ("arena_bytes", C.c_uint64), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class CPreBatch(C.Structure):
+    _fields_ = [("n_targets", C.c_uint32), ("n_recs", C.c_uint32),
+                ("tgt_tlen", C.c_void_p), ("tgt_rec_begin", C.c_void_p), ("rec_start", C.c_void_p), ("rec_strand", C.c_void_p),
+                ("rec_qlen", C.c_void_p), ("rec_tseglen", C.c_void_p), ("rec_q_off", C.c_void_p), ("rec_t_off", C.c_void_p),
+                ("arena", C.c_void_p), ("arena_bytes", C.c_uint64)]
+
+
+class PreBatch:
+    """'pre' records (reference Alignment.cpp:82-112): targets = [(tlen, [(qseq, tseq, strand '+'|'-', tstart)])]."""
+
+    def __init__(self, targets):
+        tl, rb, st, sd, ql, tl2, qo, to, chunks, pos = [], [0], [], [], [], [], [], [], [], 0
+        for tlen, recs in targets:
+            tl.append(tlen)
+            for q, t, strand, start in recs:
+                st.append(start); sd.append(1 if strand in ("-", b"-") else 0)
+                ql.append(len(q)); tl2.append(len(t))
+                qo.append(pos); chunks.append(q); pos += len(q)
+                to.append(pos); chunks.append(t); pos += len(t)
+            rb.append(len(st))
+        self.a = [np.array(x, dt) for x, dt in ((tl, np.uint32), (rb, np.uint32), (st, np.uint32), (sd, np.uint32), (ql, np.uint32),
+                                                (tl2, np.uint32), (qo, np.uint64), (to, np.uint64))]
+        self.arena = np.frombuffer(b"".join(chunks) + b"\0" * 16, np.uint8).copy()
+        self.n_targets, self.n_recs = len(tl), len(st)
+        self.cap = int(sum(ql) + sum(tl2))
+        c = CPreBatch()
+        c.n_targets, c.n_recs = self.n_targets, self.n_recs
+        (c.tgt_tlen, c.tgt_rec_begin, c.rec_start, c.rec_strand, c.rec_qlen, c.rec_tseglen, c.rec_q_off, c.rec_t_off) = [_ptr(x) for x in self.a]
+        c.arena, c.arena_bytes = _ptr(self.arena), int(self.arena.size) - 16
+        self.c = c
 
 
 class CResults(C.Structure):
@@ -92,6 +124,8 @@ def load_library():
     lib.dgc_debug_normalize.argtypes = [H, H, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.dgc_debug_graph.argtypes = [H, H, C.c_uint32, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.dgc_debug_free.argtypes = [C.c_void_p]
+    lib.dgc_submit_pre.argtypes = [H, C.POINTER(CPreBatch)]
+    lib.dgc_debug_pre_strings.argtypes = [H, C.POINTER(CPreBatch), C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 
@@ -290,6 +324,20 @@ class Consensus:
         t = Timings()
         self.lib.dgc_get_timings(self.h, C.byref(t))
         return t.as_dict()
+
+    # --- `-a`: ungapped 'pre' records, aligned on the device
+    def submit_pre(self, batch: "PreBatch"):
+        self._check(self.lib.dgc_submit_pre(self.h, C.byref(batch.c)), "dgc_submit_pre")
+        self._inflight.append(batch)
+
+    def debug_pre_strings(self, batch: "PreBatch"):
+        """[(q, t, start1)] per record as the device aligned it ((b"", b"", start) when nothing aligns)."""
+        R = batch.n_recs
+        q, t = np.zeros(batch.cap + 16, np.uint8), np.zeros(batch.cap + 16, np.uint8)
+        off, ln, st = np.zeros(R + 1, np.uint64), np.zeros(R + 1, np.uint32), np.zeros(R + 1, np.uint32)
+        self._check(self.lib.dgc_debug_pre_strings(self.h, C.byref(batch.c), q.ctypes.data, t.ctypes.data, batch.cap + 16, off.ctypes.data,
+                                                   ln.ctypes.data, st.ctypes.data), "dgc_debug_pre_strings")
+        return [(q[int(off[k]):int(off[k]) + int(ln[k])].tobytes(), t[int(off[k]):int(off[k]) + int(ln[k])].tobytes(), int(st[k])) for k in range(R)]
 
     # --- test hooks
     def debug_normalize(self, batch: PackedBatch):

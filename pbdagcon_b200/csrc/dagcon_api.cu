@@ -9,6 +9,7 @@
 #include "../../include/dagcon_b200.h"
 #include "dagcon_kernels.cuh"
 #include "daz_realign.cuh"
+#include "pre_align.cuh"
 
 #include <algorithm>
 #include <condition_variable>
@@ -138,6 +139,11 @@ struct Slot {
     dgc_batch pending{};  // copied at submit: only the arrays it points to must outlive the call
     dgc_daz_batch pending_daz{};
     bool is_daz = false;
+    dgc_pre_batch pending_pre{};
+    bool is_pre = false;
+    // `-a` alignment (pre_align.cuh)
+    DevBuf p_in, p_qoff, p_toff, p_qlen, p_tlen, p_strand, p_start, p_tglen, p_ids, p_tboff, p_tb, p_tbeg, p_tend, p_state;
+    HostBuf ph_plan;
     // dazcon realignment (daz_realign.cuh): per-overlap inputs, per-segment work arrays, edit scripts, wave slabs
     DevBuf z_aread, z_bread, z_comp, z_abpos, z_aepos, z_bbpos, z_bepos, z_troff, z_tlen, z_segb, z_eoff, z_trace, z_tgt_aread;
     DevBuf z_seg_bb, z_seg_eoff, z_seg_cnt, z_seg_neg, z_seg_ppos, z_seg_pneg, z_entries, z_vf, z_hf, z_err;
@@ -988,8 +994,11 @@ void begin_run(Slot& s) {
 
 int slot_process_daz(Slot& s, const dgc_daz_batch* b);
 
+int slot_process_pre(Slot& s, const dgc_pre_batch* b);
+
 int slot_process(Slot& s, const dgc_batch* b) {
     if (s.is_daz) return slot_process_daz(s, &s.pending_daz);
+    if (s.is_pre) return slot_process_pre(s, &s.pending_pre);
     begin_run(s);
     dgc_handle* h = s.h;
     {
@@ -1202,6 +1211,170 @@ int slot_process_daz(Slot& s, const dgc_daz_batch* b) {
     return rc;
 }
 
+// ------------------------------------------------------------------------------------------
+// dgc_submit_pre: the `-a` step on the device (pre_align.cuh), then the batch runs through the same kernels as any
+// other.  A record's gapped strings have at most qlen + tseglen columns: every offset is planned from that bound.
+int validate_pre(const dgc_pre_batch* b, std::string& err) {
+    if (!b) { err = "null batch"; return DGC_E_INVALID; }
+    if (b->n_targets && (!b->tgt_tlen || !b->tgt_rec_begin)) { err = "null target arrays"; return DGC_E_INVALID; }
+    if (b->n_recs && (!b->rec_start || !b->rec_strand || !b->rec_qlen || !b->rec_tseglen || !b->rec_q_off || !b->rec_t_off || !b->arena)) {
+        err = "null record arrays"; return DGC_E_INVALID;
+    }
+    if (b->n_targets && (b->tgt_rec_begin[0] != 0 || b->tgt_rec_begin[b->n_targets] != b->n_recs)) { err = "tgt_rec_begin is not a CSR over n_recs"; return DGC_E_INVALID; }
+    for (uint32_t t = 0; t < b->n_targets; t++) {
+        if (b->tgt_rec_begin[t + 1] < b->tgt_rec_begin[t]) { err = "tgt_rec_begin not monotone"; return DGC_E_INVALID; }
+        if (b->tgt_tlen[t] > 0x3FFFFFFFu) { err = "tlen too large"; return DGC_E_INVALID; }
+    }
+    for (uint32_t k = 0; k < b->n_recs; k++) {
+        const uint64_t nq = b->rec_qlen[k], nt = b->rec_tseglen[k];
+        if (b->rec_q_off[k] > b->arena_bytes || nq > b->arena_bytes - b->rec_q_off[k] || b->rec_t_off[k] > b->arena_bytes ||
+            nt > b->arena_bytes - b->rec_t_off[k]) { err = "record segment outside arena"; return DGC_E_INVALID; }
+        if (nq > 0x0FFFFFFFu || nt > 0x0FFFFFFFu) { err = "record too long"; return DGC_E_INVALID; }
+    }
+    return DGC_OK;
+}
+
+int build_pre_batch(Slot& s, const dgc_pre_batch* b) {
+    dgc_handle* h = s.h;
+    dgc_dbatch& db = s.db;
+    cudaStream_t st = s.stream;
+    const size_t T = b->n_targets, R = b->n_recs;
+    // plan: u64 q_out[R+1] | u64 t_out[R+1] | u64 norm_off[R+1] | u64 tb_off[R+1] | u32 tglen[R+1] | u32 ids[R+1] | u32 state[R+1]
+    CU(s.ph_plan.ensure(32 * (R + 1) + 12 * (R + 1) + 64));
+    uint64_t* p_q = s.ph_plan.as<uint64_t>();
+    uint64_t* p_t = p_q + (R + 1);
+    uint64_t* p_norm = p_t + (R + 1);
+    uint64_t* p_tb = p_norm + (R + 1);
+    uint32_t* p_tg = (uint32_t*)(p_tb + (R + 1));
+    uint32_t* p_ids = p_tg + (R + 1);
+    uint32_t* p_state = p_ids + (R + 1);
+    uint64_t arena = 0, norm = 0, raw = 0;
+    for (size_t t = 0; t < T; t++)
+        for (uint32_t k = b->tgt_rec_begin[t]; k < b->tgt_rec_begin[t + 1]; k++) {
+            const uint64_t cap = (uint64_t)b->rec_qlen[k] + b->rec_tseglen[k];
+            p_q[k] = arena; arena += (cap + 15) & ~15ull;
+            p_t[k] = arena; arena += (cap + 15) & ~15ull;
+            p_norm[k] = norm; norm += (2 * cap + 7) & ~7ull;
+            p_tg[k] = b->tgt_tlen[t];
+            raw += cap;
+        }
+    db.T = (uint32_t)T; db.A = (uint32_t)R; db.has_bb = false; db.packed4 = false; db.arena_bytes = arena; db.norm_cols = norm; db.raw_cols = raw;
+    db.h_tlen.assign(b->tgt_tlen, b->tgt_tlen + T);
+    db.h_aln_begin.assign(b->tgt_rec_begin, b->tgt_rec_begin + T + 1);
+    if (T == 0) return DGC_OK;
+    CU(db.tgt_tlen.ensure(4 * (T + 1))); CU(db.tgt_aln_begin.ensure(4 * (T + 1)));
+    CU(db.aln_start.ensure(4 * (R + 1))); CU(db.aln_len.ensure(4 * (R + 1)));
+    CU(db.aln_q_off.ensure(8 * (R + 1))); CU(db.aln_t_off.ensure(8 * (R + 1))); CU(db.aln_norm_off.ensure(8 * (R + 1)));
+    CU(db.arena.ensure(arena + 64));
+    CU(s.p_in.ensure(b->arena_bytes + 64));
+    for (DevBuf* d : {&s.p_qlen, &s.p_tlen, &s.p_strand, &s.p_start, &s.p_tglen, &s.p_ids, &s.p_tbeg, &s.p_tend, &s.p_state}) CU(d->ensure(4 * (R + 1)));
+    CU(s.p_qoff.ensure(8 * (R + 1))); CU(s.p_toff.ensure(8 * (R + 1))); CU(s.p_tboff.ensure(8 * (R + 1)));
+    span_begin(s, PH_H2D);
+    CU(cudaMemcpyAsync(db.tgt_tlen.p, b->tgt_tlen, 4 * T, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(db.tgt_aln_begin.p, b->tgt_rec_begin, 4 * (T + 1), cudaMemcpyHostToDevice, st));
+    if (R) {
+        CU(cudaMemcpyAsync(db.aln_q_off.p, p_q, 8 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db.aln_t_off.p, p_t, 8 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db.aln_norm_off.p, p_norm, 8 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_qoff.p, b->rec_q_off, 8 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_toff.p, b->rec_t_off, 8 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_qlen.p, b->rec_qlen, 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_tlen.p, b->rec_tseglen, 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_strand.p, b->rec_strand, 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_start.p, b->rec_start, 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_tglen.p, p_tg, 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(s.p_in.p, b->arena, b->arena_bytes, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(s.p_state.p, 0, 4 * R, st));
+    }
+    span_end(s);
+    CU(cudaStreamSynchronize(st));
+    release_h2d_turn_now(h, s.seq + 1);
+    if (R == 0) return DGC_OK;
+    PreArgs a;
+    a.rec_start = s.p_start.as<u32>(); a.rec_tlen = s.p_tglen.as<u32>(); a.aln_start = db.aln_start.as<u32>();
+    a.arena_in = s.p_in.as<u8>(); a.q_off = s.p_qoff.as<u64>(); a.t_off = s.p_toff.as<u64>(); a.q_len = s.p_qlen.as<u32>(); a.t_len = s.p_tlen.as<u32>();
+    a.strand = s.p_strand.as<u32>(); a.tb_off = s.p_tboff.as<u64>();
+    a.arena_out = db.arena.as<u8>(); a.out_q_off = db.aln_q_off.as<u64>(); a.out_t_off = db.aln_t_off.as<u64>(); a.out_len = db.aln_len.as<u32>();
+    a.t_begin = s.p_tbeg.as<u32>(); a.t_end = s.p_tend.as<u32>(); a.state = s.p_state.as<u32>();
+    // ---- bands 64, 128, ...: the records whose path came too close to the band's edge go round again
+    std::vector<uint32_t> pending(R);
+    for (size_t k = 0; k < R; k++) pending[k] = (uint32_t)k;
+    const uint64_t tb_budget = 8ull << 30;
+    span_begin(s, PH_DAZ);   // reported as ms_realign
+    for (uint32_t band = 64; !pending.empty(); band *= 2) {
+        if (band > PA_MAX_BAND) {   // hopeless records (unrelated sequences longer than the widest band): nothing aligns
+            break;
+        }
+        const uint32_t warps = band <= 512 ? 4u : 1u;
+        const size_t smem = (size_t)warps * 2 * (2 * band + 1 + 2 * PA_G) * sizeof(int);
+        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k_pre_align, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        size_t done = 0;
+        while (done < pending.size()) {   // waves that fit the move-matrix budget
+            uint64_t tb = 0;
+            size_t n = 0;
+            while (done + n < pending.size()) {
+                const uint32_t k = pending[done + n];
+                const uint64_t full = (uint64_t)std::max(b->rec_qlen[k], b->rec_tseglen[k]) + 1;
+                const uint64_t W = 2 * std::min<uint64_t>(band, full) + 1;
+                const uint64_t need = (((uint64_t)b->rec_qlen[k] + 1) * W + 15) & ~15ull;
+                if (n && tb + need > tb_budget) break;
+                p_tb[n] = tb; p_ids[n] = k;
+                tb += need;
+                n++;
+            }
+            CU(s.p_tb.ensure(tb + 64));
+            CU(s.p_ids.ensure(4 * (n + 1)));
+            CU(cudaMemcpyAsync(s.p_tboff.p, p_tb, 8 * n, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(s.p_ids.p, p_ids, 4 * n, cudaMemcpyHostToDevice, st));
+            a.rec_ids = s.p_ids.as<u32>(); a.n_launch = (u32)n; a.band = band; a.warps = warps; a.tb = s.p_tb.as<u8>();
+            k_pre_align<<<(unsigned)((n + warps - 1) / warps), warps * 32, smem, st>>>(a);
+            s.tm.launches++;
+            CU(cudaGetLastError());
+            CU(cudaStreamSynchronize(st));   // p_tb / p_ids are reused by the next wave
+            done += n;
+        }
+        CU(cudaMemcpyAsync(p_state, s.p_state.p, 4 * R, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        std::vector<uint32_t> next;
+        for (uint32_t k : pending)
+            if (p_state[k] == 2) next.push_back(k);
+        pending.swap(next);
+    }
+    if (!pending.empty()) {   // beyond the widest band: zero-column alignments (they still count towards the target's coverage)
+        for (uint32_t k : pending) p_state[k] = 3;
+        std::vector<uint32_t> zero(R, 0), st1(R, 0);
+        CU(cudaMemcpyAsync(zero.data(), db.aln_len.p, 4 * R, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(st1.data(), db.aln_start.p, 4 * R, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        for (uint32_t k : pending) { zero[k] = 0; st1[k] = b->rec_start[k] + 1; }
+        CU(cudaMemcpyAsync(db.aln_len.p, zero.data(), 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db.aln_start.p, st1.data(), 4 * R, cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    span_end(s);
+    return DGC_OK;
+}
+
+int slot_process_pre(Slot& s, const dgc_pre_batch* b) {
+    begin_run(s);
+    dgc_handle* h = s.h;
+    {
+        std::unique_lock<std::mutex> lk(h->h2d_mu);
+        h->h2d_cv.wait(lk, [&] { return h->h2d_turn == s.seq; });
+    }
+    int rc = build_pre_batch(s, b);
+    bool released;
+    {
+        std::lock_guard<std::mutex> lk(h->h2d_mu);
+        released = h->h2d_turn > s.seq;
+    }
+    if (!released) release_h2d_turn_now(h, s.seq + 1);
+    if (rc == DGC_OK) rc = run_pipeline(s, s.db, 2, 0xFFFFFFFFu);
+    cudaStreamSynchronize(s.stream);
+    finish_timings(s);
+    return rc;
+}
+
 void worker_main(Slot* sp) {
     Slot& s = *sp;
     cudaSetDevice(s.h->device);
@@ -1306,9 +1479,12 @@ int dgc_destroy(dgc_handle* h) {
                           &s.rec_off, &s.pos_off, &s.pool_cap, &s.t_pool_top, &s.cons_off, &s.frag_off, &s.frag_cap, &s.gs_off, &s.gs_cap,
                           &s.rec, &s.cons, &s.frags, &s.gscratch, &s.gacc, &s.out_cons, &s.out_frags, &s.z_aread, &s.z_bread, &s.z_comp,
                           &s.z_abpos, &s.z_aepos, &s.z_bbpos, &s.z_bepos, &s.z_troff, &s.z_tlen, &s.z_segb, &s.z_eoff, &s.z_trace, &s.z_tgt_aread,
-                          &s.z_seg_bb, &s.z_seg_eoff, &s.z_seg_cnt, &s.z_seg_neg, &s.z_seg_ppos, &s.z_seg_pneg, &s.z_entries, &s.z_vf, &s.z_hf, &s.z_err})
+                          &s.z_seg_bb, &s.z_seg_eoff, &s.z_seg_cnt, &s.z_seg_neg, &s.z_seg_ppos, &s.z_seg_pneg, &s.z_entries, &s.z_vf, &s.z_hf, &s.z_err,
+                          &s.p_in, &s.p_qoff, &s.p_toff, &s.p_qlen, &s.p_tlen, &s.p_strand, &s.p_start, &s.p_tglen, &s.p_ids, &s.p_tboff, &s.p_tb,
+                          &s.p_tbeg, &s.p_tend, &s.p_state})
             b->release();
         s.zh_plan.release();
+        s.ph_plan.release();
         for (HostBuf* b : {&s.h_norm_off, &s.hp_plan_in, &s.hp_plan_out, &s.r_status, &s.r_cons_coff, &s.r_frag_coff, &s.r_totals,
                            &s.r_cons, &s.r_frags, &s.r_nfrag})
             b->release();
@@ -1351,6 +1527,7 @@ int dgc_submit(dgc_handle* h, const dgc_batch* batch) {
         s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
         s.pending = *batch;
         s.is_daz = false;
+        s.is_pre = false;
         s.seq = h->submitted;
         s.state = Slot::QUEUED;
         s.cv.notify_all();
@@ -1427,6 +1604,7 @@ int dgc_submit_daz(dgc_handle* h, const dgc_daz_batch* batch) {
         s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
         s.pending_daz = *batch;
         s.is_daz = true;
+        s.is_pre = false;
         s.seq = h->submitted;
         s.state = Slot::QUEUED;
         s.cv.notify_all();
@@ -1464,6 +1642,72 @@ int dgc_debug_daz_strings(dgc_handle* h, const dgc_daz_batch* batch, uint8_t* ou
         out_off[k] = pos; out_len[k] = ln[k];
         e = cudaMemcpy(out_q + pos, (const u8*)s.db.arena.p + qo[k], ln[k], cudaMemcpyDeviceToHost);
         if (e == cudaSuccess) e = cudaMemcpy(out_t + pos, (const u8*)s.db.arena.p + to[k], ln[k], cudaMemcpyDeviceToHost);
+        pos += ln[k];
+    }
+    if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return DGC_E_CUDA; }
+    return DGC_OK;
+}
+
+int dgc_submit_pre(dgc_handle* h, const dgc_pre_batch* batch) {
+    if (!h) return DGC_E_INVALID;
+    int rc = validate_pre(batch, h->err);
+    if (rc) return rc;
+    int si = -1;
+    {
+        std::lock_guard<std::mutex> lk(h->q_mu);
+        if (h->inflight.size() >= (size_t)DGC_MAX_INFLIGHT) { h->err = "too many batches in flight: collect first"; return DGC_E_STATE; }
+        for (int i = 0; i < NSLOT && si < 0; i++)
+            if (!h->busy[i]) si = i;
+        h->busy[si] = true;
+        h->inflight.push_back(si);
+    }
+    Slot& s = h->slots[si];
+    {
+        std::unique_lock<std::mutex> lk(s.mu);
+        s.cv.wait(lk, [&] { return s.state == Slot::IDLE || s.state == Slot::DONE; });
+        s.pending_pre = *batch;
+        s.is_pre = true;
+        s.is_daz = false;
+        s.seq = h->submitted;
+        s.state = Slot::QUEUED;
+        s.cv.notify_all();
+    }
+    h->submitted++;
+    return DGC_OK;
+}
+
+int dgc_debug_pre_strings(dgc_handle* h, const dgc_pre_batch* batch, uint8_t* out_q, uint8_t* out_t, uint64_t out_cap,
+                          uint64_t* out_off, uint32_t* out_len, uint32_t* out_start) {
+    if (!h || !batch || !out_off || !out_len || !out_start) return DGC_E_INVALID;
+    if (h->submitted != h->collected) { h->err = "debug call while batches are in flight"; return DGC_E_STATE; }
+    int rc = validate_pre(batch, h->err);
+    if (rc) return rc;
+    cudaSetDevice(h->device);
+    Slot& s = h->slots[0];
+    begin_run(s);
+    const uint64_t turn = h->h2d_turn;
+    s.seq = turn;
+    rc = build_pre_batch(s, batch);
+    release_h2d_turn_now(h, turn);
+    if (rc) { h->err = s.err; return rc; }
+    const size_t R = batch->n_recs;
+    std::vector<uint64_t> qo(R), to(R);
+    std::vector<uint32_t> ln(R);
+    cudaError_t e = cudaSuccess;
+    if (R) {
+        e = cudaMemcpy(qo.data(), s.db.aln_q_off.p, 8 * R, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(to.data(), s.db.aln_t_off.p, 8 * R, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(ln.data(), s.db.aln_len.p, 4 * R, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(out_start, s.db.aln_start.p, 4 * R, cudaMemcpyDeviceToHost);
+    }
+    uint64_t pos = 0;
+    for (size_t k = 0; k < R && e == cudaSuccess; k++) {
+        if (pos + ln[k] > out_cap) { h->err = "output buffers too small"; return DGC_E_INVALID; }
+        out_off[k] = pos; out_len[k] = ln[k];
+        if (ln[k]) {
+            e = cudaMemcpy(out_q + pos, (const u8*)s.db.arena.p + qo[k], ln[k], cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess) e = cudaMemcpy(out_t + pos, (const u8*)s.db.arena.p + to[k], ln[k], cudaMemcpyDeviceToHost);
+        }
         pos += ln[k];
     }
     if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return DGC_E_CUDA; }

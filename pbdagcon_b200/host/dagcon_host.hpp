@@ -113,6 +113,14 @@ struct DazPayload {
     dgc_daz_batch view() const;
 };
 
+// The `-a` form of a batch (include/dagcon_b200.h: dgc_pre_batch): ungapped 'pre' records; aligned on the device.
+struct PrePayload {
+    std::vector<uint32_t> tgt_tlen, tgt_rec_begin{0}, rec_start, rec_strand, rec_qlen, rec_tseglen;
+    std::vector<uint64_t> rec_q_off, rec_t_off;
+    std::vector<uint8_t> arena;
+    dgc_pre_batch view() const;
+};
+
 // A packed batch in host memory (pinned when `pinned`), laid out as include/dagcon_b200.h: dgc_batch.
 class HostBatch {
 public:
@@ -142,6 +150,7 @@ public:
     std::vector<std::string> ids;   // Alignment::id of alns[0] per target
     uint64_t seq = 0;               // position in the input stream (batch number)
     std::unique_ptr<DazPayload> daz;   // set: submit with dgc_submit_daz (n_targets and ids are filled, the arrays below unused)
+    std::unique_ptr<PrePayload> pre;   // set: submit with dgc_submit_pre (likewise)
 
     uint32_t* tgt_tlen = nullptr;
     uint32_t* tgt_aln_begin = nullptr;
@@ -185,6 +194,7 @@ struct ProgramOpts {
     size_t batchTargets = 256;          // a batch closes at this many targets or this much input text: small enough
     size_t batchBytes = 192ull << 20;   // that several are being packed at once and the page-locked ring stays small
     bool stats = false;
+    bool hostAlign = false;             // -a with --host-align: align 'pre' records on the host threads instead of on the device
     bool asciiWire = false;             // --ascii-wire: send the alignment strings as ASCII instead of 4-bit codes
 };
 

@@ -28,6 +28,7 @@ void usage(FILE* f) {
           "   --gpus <int>               GPUs to use (default: all visible)\n"
           "   --batch-targets <int>, --batch-mb <int>   targets / MiB of alignment text per GPU batch\n"
           "   --stats                    print a JSON throughput line on stderr\n"
+          "   --host-align               with -a: align the 'pre' records on the host threads instead of on the GPU\n"
           "   --ascii-wire               send the alignment strings to the GPU as ASCII (default: 4-bit codes, half the bytes)\n"
           "   <either file path or stdin>  (required)  Input data (BLASR -m5 sorted by target; '-' = stdin)\n\n"
           "   PBI consensus module, B200 build\n",
@@ -60,6 +61,7 @@ int main(int argc, char** argv) {
         if (a == "-v" || a == "--verbose") { o.verbose = true; continue; }
         if (a == "--stats") { o.stats = true; continue; }
         if (a == "--ascii-wire") { o.asciiWire = true; continue; }
+        if (a == "--host-align") { o.hostAlign = true; continue; }
         // value flags: "-j 4", "-j4", "--threads 4", "--threads=4"
         std::string name = a, val;
         bool has_val = false;

@@ -282,6 +282,34 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); break; }
                     if (!units.pop(u)) { free_batches.push(std::move(hb)); break; }  // hand the batch on: another packer may be waiting for one just to find the input exhausted
                     try {
+                        hb->pre.reset();
+                        if (fmt == TextFormat::PRE && !o.hostAlign && pinned) {
+                            // -a: the records go to the device as they are (ungapped segments); dgc_submit_pre aligns them
+                            hb->clear();
+                            hb->seq = u->seq;
+                            hb->pre.reset(new PrePayload());
+                            PrePayload& z = *hb->pre;
+                            z.arena.reserve(u->bytes + 64 * u->lines.size());
+                            for (size_t t = 0; t + 1 < u->tgt_begin.size(); t++) {
+                                bool first = true;
+                                for (uint32_t li = u->tgt_begin[t]; li < u->tgt_begin[t + 1]; li++) {
+                                    LineFields f;
+                                    if (!split_line(u->lines[li].first, u->lines[li].second, fmt, f)) continue;
+                                    if (first) { z.tgt_tlen.push_back(f.tlen); hb->ids.emplace_back(f.id, f.id_len); first = false; }
+                                    z.rec_start.push_back(f.start);
+                                    z.rec_strand.push_back(f.strand == '-' ? 1u : 0u);
+                                    z.rec_qlen.push_back((uint32_t)f.q_len); z.rec_tseglen.push_back((uint32_t)f.t_len);
+                                    z.rec_q_off.push_back(z.arena.size()); z.arena.insert(z.arena.end(), f.q, f.q + f.q_len);
+                                    z.rec_t_off.push_back(z.arena.size()); z.arena.insert(z.arena.end(), f.t, f.t + f.t_len);
+                                }
+                                if (!first) z.tgt_rec_begin.push_back((uint32_t)z.rec_start.size());
+                            }
+                            hb->n_targets = (uint32_t)z.tgt_tlen.size();
+                            hb->n_alns = (uint32_t)z.rec_start.size();
+                            u.reset();
+                            outbox.put(std::move(hb));
+                            continue;
+                        }
                         std::vector<PreAligned> aligned;
                         if (fmt == TextFormat::PRE) align_unit(*u, aligned);
                         std::vector<std::pair<const char*, size_t>> lines;
@@ -435,6 +463,7 @@ int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunSta
         if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s submit batch %llu (%u targets, %.1f MB) to GPU %d\n", prog, since(t0), (unsigned long long)seq, hb->n_targets, hb->arena_bytes / 1e6, g);
         int c;
         if (hb->daz) { const dgc_daz_batch zb = hb->daz->view(); c = dgc_submit_daz(hs[(size_t)g], &zb); }
+        else if (hb->pre) { const dgc_pre_batch pb = hb->pre->view(); c = dgc_submit_pre(hs[(size_t)g], &pb); }
         else { const dgc_batch b = hb->view(); c = dgc_submit(hs[(size_t)g], &b); }
         if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); feed.recycle(std::move(hb)); continue; }
         on_gpu[(size_t)g]++;

@@ -377,6 +377,17 @@ dgc_batch HostBatch::view() const {
     return b;
 }
 
+dgc_pre_batch PrePayload::view() const {
+    dgc_pre_batch b{};
+    b.n_targets = (uint32_t)tgt_tlen.size();
+    b.n_recs = (uint32_t)rec_start.size();
+    b.tgt_tlen = tgt_tlen.data(); b.tgt_rec_begin = tgt_rec_begin.data();
+    b.rec_start = rec_start.data(); b.rec_strand = rec_strand.data(); b.rec_qlen = rec_qlen.data(); b.rec_tseglen = rec_tseglen.data();
+    b.rec_q_off = rec_q_off.data(); b.rec_t_off = rec_t_off.data();
+    b.arena = arena.data(); b.arena_bytes = arena.size();
+    return b;
+}
+
 dgc_daz_batch DazPayload::view() const {
     dgc_daz_batch b{};
     b.n_targets = (uint32_t)tgt_aread.size();
