@@ -191,8 +191,8 @@ struct ProgramOpts {
                                     // instead of on the device
     // dispatcher
     int gpus = 0;           // 0 = all visible devices
-    size_t batchTargets = 256;          // a batch closes at this many targets or this much input text: small enough
-    size_t batchBytes = 192ull << 20;   // that several are being packed at once and the page-locked ring stays small
+    size_t batchTargets = 1024;         // a batch closes at this many targets or this much input text (the first four
+    size_t batchBytes = 768ull << 20;   // units at a quarter of it): several are packed at once, the page-locked ring stays small
     bool stats = false;
     bool hostAlign = false;             // -a with --host-align: align 'pre' records on the host threads instead of on the device
     bool asciiWire = false;             // --ascii-wire: send the alignment strings as ASCII instead of 4-bit codes
