@@ -202,7 +202,11 @@ struct RunStats {
     uint64_t targets_in = 0, targets_dropped = 0, alignments = 0, input_bytes = 0;
     uint64_t batches = 0, records = 0, bases = 0;
     double seconds = 0, scan_seconds = 0;
+    // where the host front spends its time (--stats): the scanner cutting lines (without its waits for free slots),
+    // the packers' parsing + packing summed over threads, and page-locking batch buffers
+    double scan_cut_seconds = 0, pack_seconds = 0, pin_seconds = 0;
 };
+extern double g_pin_seconds;   // accumulated by HostBatch::alloc (process-wide; read by the pipelines)
 
 // Reads `opts.input` ("-" = stdin), runs every target through the GPUs, writes FASTA records to `out`
 // in input-target order.  Returns 0 or a DGC_E_* code (message in `err`).

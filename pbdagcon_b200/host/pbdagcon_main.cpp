@@ -98,10 +98,12 @@ int main(int argc, char** argv) {
     if (o.stats || o.verbose)
         fprintf(stderr,
                 "{\"targets\": %llu, \"targets_dropped\": %llu, \"alignments\": %llu, \"input_bytes\": %llu, \"batches\": %llu, "
-                "\"records\": %llu, \"bases\": %llu, \"seconds\": %.4f, \"scan_seconds\": %.4f, \"mbp_per_s\": %.3f, \"targets_per_s\": %.1f}\n",
+                "\"records\": %llu, \"bases\": %llu, \"seconds\": %.4f, \"scan_seconds\": %.4f, \"scan_cut_seconds\": %.4f, \"pack_thread_seconds\": %.4f, "
+                "\"pin_seconds\": %.4f, \"mbp_per_s\": %.3f, \"targets_per_s\": %.1f}\n",
                 (unsigned long long)st.targets_in, (unsigned long long)st.targets_dropped, (unsigned long long)st.alignments,
                 (unsigned long long)st.input_bytes, (unsigned long long)st.batches, (unsigned long long)st.records,
-                (unsigned long long)st.bases, st.seconds, st.scan_seconds, st.bases / 1e6 / (st.seconds > 0 ? st.seconds : 1),
+                (unsigned long long)st.bases, st.seconds, st.scan_seconds, st.scan_cut_seconds, st.pack_seconds, st.pin_seconds,
+                st.bases / 1e6 / (st.seconds > 0 ? st.seconds : 1),
                 st.targets_in / (st.seconds > 0 ? st.seconds : 1));
     // Every handle is destroyed and every record written: leave without the CUDA runtime's own process teardown
     // (unmapping the page-locked ring and the context costs several hundred ms that buy nothing at exit).

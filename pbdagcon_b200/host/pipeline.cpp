@@ -158,10 +158,12 @@ private:
                     if (scan_err.empty()) scan_err = fe.msg;
                 }
             };
+            const auto tc0 = std::chrono::steady_clock::now();
             std::vector<std::thread> th;
             for (int i = 1; i < nscan; i++) th.emplace_back(work, i);
             work(0);
             for (auto& t : th) t.join();
+            st_.scan_cut_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - tc0).count();
             if (!scan_err.empty()) throw M5Exception::FormatError{scan_err};
             for (auto& part : parts)
                 for (const LineRec& r : part) take_scanned(blk, r.p, r.n, r.id_off == 0xFFFFFFFFu ? nullptr : r.p + r.id_off, r.idn);
@@ -336,6 +338,11 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                         if (!take_batch(hb)) break;
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); break; }
                     if (!units.pop(u)) { free_batches.push(std::move(hb)); break; }  // hand the batch on: another packer may be waiting for one just to find the input exhausted
+                    const auto tp0 = std::chrono::steady_clock::now();
+                    struct PackTimer {
+                        Front* f; std::chrono::steady_clock::time_point t0;
+                        ~PackTimer() { const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); std::lock_guard<std::mutex> lk(f->err_mu); f->st.pack_seconds += dt; }
+                    } pack_timer{this, tp0};
                     try {
                         hb->pre.reset();
                         if (fmt == TextFormat::PRE && !o.hostAlign && pinned) {
@@ -548,6 +555,7 @@ int run_text_pipeline(const ProgramOpts& opts, FILE* out, RunStats& stats, std::
     int rc = dispatch_batches(opts, feed, out, stats, err, false);
     fr.stop();
     if (!rc && fr.rc) { rc = fr.rc; err = fr.err; }
+    stats.pin_seconds = g_pin_seconds;
     stats.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return rc;
 }

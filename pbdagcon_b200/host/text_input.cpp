@@ -4,7 +4,9 @@
 #include <algorithm>
 #include <cerrno>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
+#include <mutex>
 
 #include "dagcon_host.hpp"
 
@@ -103,10 +105,19 @@ void revcomp_into(const char* src, size_t n, uint8_t* dst) {
 }
 
 // ------------------------------------------------------------------------------------------ HostBatch
+double g_pin_seconds = 0;
+static std::mutex g_pin_mu;
+
 void* HostBatch::alloc(size_t bytes) {
     void* p = nullptr;
     if (pinned_) {
+        const auto t0 = std::chrono::steady_clock::now();
         if (dgc_host_alloc(&p, bytes) != DGC_OK) throw std::bad_alloc();
+        if (bytes > (1u << 20)) {
+            const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            std::lock_guard<std::mutex> lk(g_pin_mu);
+            g_pin_seconds += dt;
+        }
     } else {
         p = malloc(bytes ? bytes : 1);
         if (!p) throw std::bad_alloc();
