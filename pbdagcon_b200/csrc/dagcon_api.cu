@@ -12,6 +12,7 @@
 #include "pre_align.cuh"
 
 #include <algorithm>
+#include <chrono>
 #include <condition_variable>
 #include <deque>
 #include <cstdio>
@@ -195,6 +196,15 @@ namespace {
             return DGC_E_CUDA;                                                                     \
         }                                                                                          \
     } while (0)
+
+// DGC_TRACE=1: host-side timestamps of a slot's work on stderr (where a batch's wall time goes besides its kernels)
+static const bool g_trace = getenv("DGC_TRACE") && getenv("DGC_TRACE")[0] == '1';
+static const auto g_t0 = std::chrono::steady_clock::now();
+static void trace(const Slot& s, const char* what) {
+    if (!g_trace) return;
+    fprintf(stderr, "dgc-trace %.4f s slot %d seq %llu: %s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - g_t0).count(),
+            s.index, (unsigned long long)s.seq, what);
+}
 
 void span_begin(Slot& s, int ph) {
     cudaEvent_t a = s.events.get(), b = s.events.get();
@@ -571,6 +581,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
         s.results.tgt_frag_begin = s.res_frag_begin.data();
         return DGC_OK;
     }
+    trace(s, "run_pipeline: begin");
     int rc = ensure_alignment_arrays(s, db);
     if (rc) return rc;
     for (DevBuf* b : {&s.t_status, &s.t_V, &s.t_E, &s.t_ne, &s.t_nv, &s.t_cons_len, &s.t_nfrag, &s.frag_cap, &s.gs_cap, &s.t_frag_coff,
@@ -581,6 +592,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     CU(s.totals.ensure(64));
     CU(s.hp_plan_in.ensure(20 * (T + 1) + 16));
     CU(s.hp_plan_out.ensure(64 * (T + 1)));
+    trace(s, "run_pipeline: small buffers + norm allocated");
 
     span_begin(s, PH_NORM);
     rc = launch_normalize(s, db);
@@ -601,6 +613,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     CU(cudaMemcpyAsync(hp_E, s.t_E.p, 4 * T, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(hp_cols, s.t_cols.p, 8 * T, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    trace(s, "run_pipeline: normalise + plan done");
 
     // ---- host planning: arena offsets per target (128-byte units), chunks that fit the scratch budget
     uint64_t* p_rec = s.hp_plan_out.as<uint64_t>();
@@ -655,6 +668,7 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     CU(s.cons.ensure(mCons + 64)); CU(s.frags.ensure(8 * mFrag + 64)); CU(s.gscratch.ensure(4 * mGs + 64));
     if (need_gacc) CU(s.gacc.ensure(ACC_BYTES * mPos + 64));
     CU(s.out_cons.ensure(out_cons_cap + 64)); CU(s.out_frags.ensure(8 * out_frag_cap + 64));
+    trace(s, "run_pipeline: graph arenas allocated");
     CU(cudaMemcpyAsync(s.rec_off.p, p_rec, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.pos_off.p, p_pos, 8 * T, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.cons_off.p, p_cons, 8 * T, cudaMemcpyHostToDevice, st));
@@ -677,7 +691,10 @@ int run_pipeline(Slot& s, dgc_dbatch& db, int stop_after, uint32_t only_target) 
     rc = retry_pool_failures(s, db, stop_after);
     if (rc) return rc;
     if (stop_after < 2) { CU(cudaStreamSynchronize(st)); return DGC_OK; }
-    return fetch_results(s, db);
+    trace(s, "run_pipeline: kernels enqueued");
+    rc = fetch_results(s, db);
+    trace(s, "run_pipeline: results fetched");
+    return rc;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1011,8 +1028,10 @@ int slot_process(Slot& s, const dgc_batch* b) {
     if (split_pieces(b, want, pieces)) {
         rc = run_staged(s, b, pieces);  // hands the link to the next batch as soon as its own bytes have landed
     } else {
+        trace(s, "slot: got the H2D turn");
         rc = upload_batch(s, b, s.db, true);
         cudaStreamSynchronize(s.stream);
+        trace(s, "slot: batch uploaded");
         release_h2d_turn_now(h, s.seq + 1);
         if (rc == DGC_OK) rc = run_pipeline(s, s.db, 2, 0xFFFFFFFFu);
     }
