@@ -27,64 +27,38 @@ namespace {
 
 thread_local std::string g_create_error;
 
-// Device buffers come from the device's stream-ordered pool when the calling thread has named a stream
-// (tls_alloc_stream: the slot workers do): growing one is then a cudaFreeAsync + cudaMallocAsync on that stream and
-// never the device-wide synchronisation of cudaFree, which would park the caller behind every other slot's running
-// graph sweep (~100 ms each).  The pool keeps what is freed (release threshold = max), so steady-state batches
-// allocate nothing.  Without a named stream (dgc_upload, the debug hooks) plain cudaMalloc / cudaFree are used.
-thread_local cudaStream_t tls_alloc_stream = nullptr;
-
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
-    cudaStream_t owner = nullptr;   // stream the block was allocated on (nullptr: cudaMalloc)
-    void drop() {
-        if (!p) return;
-        if (owner) cudaFreeAsync(p, owner); else cudaFree(p);
-        p = nullptr; cap = 0; owner = nullptr;
-    }
-    static void trim_pool() {   // hand the pool's cached blocks back to the driver (a plain cudaMalloc cannot use them)
-        int dev = 0;
-        cudaMemPool_t pool;
-        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-            cudaDeviceSynchronize();
-            cudaMemPoolTrimTo(pool, 0);
-        }
-        cudaGetLastError();
-    }
-    cudaError_t grab(size_t want) {
-        cudaStream_t st = tls_alloc_stream;
-        cudaError_t e = st ? cudaMallocAsync(&p, want, st) : cudaMalloc(&p, want);
-        if (e == cudaErrorMemoryAllocation) {   // memory may sit in the other allocator's cache: flush it and try once more
-            cudaGetLastError();
-            trim_pool();
-            e = st ? cudaMallocAsync(&p, want, st) : cudaMalloc(&p, want);
-        }
-        if (e == cudaSuccess) { cap = want; owner = st; } else { p = nullptr; cap = 0; owner = nullptr; }
-        return e;
-    }
+    // (A stream-ordered variant -- cudaMallocAsync / cudaFreeAsync on the slot's stream, to keep a growing buffer's
+    // cudaFree from waiting behind the other slots' sweeps -- was measured in round 2 and rejected: the pool's own
+    // growth made the CLI's first batches slower, 2000 targets in 2.1-3.6 s against 1.0 s; profiles/r02_cli_alloc.txt.)
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
-        drop();
-        cudaError_t e = grab(bytes + bytes / 4 + 256);
-        if (e != cudaSuccess) { cudaGetLastError(); e = grab(bytes + 256); }
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { cudaGetLastError(); e = cudaMalloc(&p, bytes + 256); want = bytes + 256; }
+        if (e == cudaSuccess) cap = want;
         return e;
     }
     // Grow without losing the first `live` bytes.  `st` is the stream whose kernels wrote those bytes: the copy is
-    // enqueued behind them on that stream and has finished before the old buffer is released (the slot streams are
+    // enqueued behind them on that stream and has finished before the old buffer is freed (the slot streams are
     // cudaStreamNonBlocking, so a copy on the legacy default stream would NOT be ordered after them).
     cudaError_t ensure_keep(size_t bytes, size_t live, cudaStream_t st) {
         if (bytes <= cap) return cudaSuccess;
-        DevBuf nb;
-        cudaError_t e = nb.grab(bytes + bytes / 4 + 256);
+        void* np = nullptr;
+        const size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&np, want);
         if (e != cudaSuccess) return e;
-        if (p && live) e = cudaMemcpyAsync(nb.p, p, std::min(live, cap), cudaMemcpyDeviceToDevice, st);
+        if (p && live) e = cudaMemcpyAsync(np, p, std::min(live, cap), cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        drop();
-        p = nb.p; cap = nb.cap; owner = nb.owner;
+        if (p) cudaFree(p);
+        p = np; cap = want;
         return e;
     }
-    void release() { drop(); }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
     template <class T> T* as() const { return (T*)p; }
 };
 struct HostBuf {  // pinned
@@ -803,10 +777,6 @@ int run_staged(Slot& s, const dgc_batch* b, std::vector<Piece>& pieces) {
     int rc = upload_batch(s, b, db, true, false);  // the small arrays, on the compute stream
     if (rc) return fail(rc);
     {
-        // the batch arena was (re)allocated in the compute stream's order: the copy stream may touch it only behind that
-        cudaEvent_t ea = s.events.get();
-        cudaEventRecord(ea, st);
-        cudaStreamWaitEvent(cs, ea, 0);
         cudaEvent_t e0 = s.events.get(), e1 = s.events.get();
         cudaEventRecord(e0, cs);
         for (auto& p : pieces) {
@@ -1436,7 +1406,6 @@ int slot_process_pre(Slot& s, const dgc_pre_batch* b) {
 void worker_main(Slot* sp) {
     Slot& s = *sp;
     cudaSetDevice(s.h->device);
-    tls_alloc_stream = s.stream;   // this thread's device buffers come from the stream-ordered pool
     std::unique_lock<std::mutex> lk(s.mu);
     for (;;) {
         s.cv.wait(lk, [&] { return s.state == Slot::QUEUED || s.state == Slot::STOP; });
@@ -1514,13 +1483,6 @@ int dgc_create(const dgc_opts* opts, dgc_handle** out) {
             return DGC_E_CUDA;
         }
     }
-    {   // keep freed blocks in the pool instead of handing them back to the driver at every synchronisation
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, opts->device) == cudaSuccess) {
-            uint64_t keep = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-        } else cudaGetLastError();
-    }
     for (int i = 0; i < NSLOT; i++) h->slots[i].th = std::thread(worker_main, &h->slots[i]);
     *out = h;
     return DGC_OK;
@@ -1559,7 +1521,6 @@ int dgc_destroy(dgc_handle* h) {
         if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
     }
     h->daz_bases.release(); h->daz_boff.release(); h->daz_rlen.release();
-    DevBuf::trim_pool();   // the next handle (or a cudaMalloc caller in this process) finds the memory free
     delete h;
     return DGC_OK;
 }
