@@ -24,7 +24,11 @@ for s in $STEPS; do
       for k in ${NCU_KERNELS:-k_merge_best2 k_build_graph2 k_normalize_warp}; do
         timeout 1200 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -f -o gpurun_out/${TAG}_full10k_$k $B > gpurun_out/${TAG}_ncu_full10k_$k.log 2>&1
         echo "ncu $k rc=$?"
-      done ;;
+        ncu -i gpurun_out/${TAG}_full10k_$k.ncu-rep --page details --csv > gpurun_out/${TAG}_full10k_${k}_details.csv 2>/dev/null
+        python profiles/ncu_by_line.py gpurun_out/${TAG}_full10k_$k.ncu-rep $k 45 > gpurun_out/${TAG}_full10k_${k}_by_line.txt 2>/dev/null
+      done
+      python profiles/make_traffic.py ${TAG} 2 10000 > gpurun_out/${TAG}_traffic.log 2>&1 && cp profiles/traffic.json gpurun_out/${TAG}_traffic.json
+      rm -f gpurun_out/${TAG}_full10k_*.ncu-rep ;;
     cli)
       python - <<'PY'
 import time, pbdagcon_b200.synth as s
