@@ -327,11 +327,11 @@ class Dist:
 
 
 def kernel_src_sha():
-    """Hash of the CUDA sources: profiles/traffic.json records the one its ncu capture was taken on."""
+    """Hash of the kernel sources (csrc/*.cuh): profiles/traffic.json records the one its ncu capture was taken on."""
     h = hashlib.sha256()
     d = os.path.join(ROOT, "pbdagcon_b200", "csrc")
     for f in sorted(os.listdir(d)):
-        if f.endswith((".cu", ".cuh")):
+        if f.endswith(".cuh"):
             h.update(open(os.path.join(d, f), "rb").read())
     return h.hexdigest()[:16]
 

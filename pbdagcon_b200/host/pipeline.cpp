@@ -26,6 +26,16 @@
 #include "dagcon_host.hpp"
 #include "channels.hpp"
 
+// NVTX ranges (header-only; no cost without a tool attached): a timeline capture of the CLI shows where its wall time goes
+#if __has_include(<nvtx3/nvToolsExt.h>)
+#include <nvtx3/nvToolsExt.h>
+#define DGH_RANGE_PUSH(name) nvtxRangePushA(name)
+#define DGH_RANGE_POP() nvtxRangePop()
+#else
+#define DGH_RANGE_PUSH(name) ((void)0)
+#define DGH_RANGE_POP() ((void)0)
+#endif
+
 namespace dgh {
 namespace {
 
@@ -159,10 +169,12 @@ private:
                 }
             };
             const auto tc0 = std::chrono::steady_clock::now();
+            DGH_RANGE_PUSH("cut lines");
             std::vector<std::thread> th;
             for (int i = 1; i < nscan; i++) th.emplace_back(work, i);
             work(0);
             for (auto& t : th) t.join();
+            DGH_RANGE_POP();
             st_.scan_cut_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - tc0).count();
             if (!scan_err.empty()) throw M5Exception::FormatError{scan_err};
             for (auto& part : parts)
@@ -339,9 +351,10 @@ struct Front {  // scanner + packers, shared by pack_text and run_text_pipeline
                     } catch (const std::exception& e) { fail(DGC_E_NOMEM, e.what()); break; }
                     if (!units.pop(u)) { free_batches.push(std::move(hb)); break; }  // hand the batch on: another packer may be waiting for one just to find the input exhausted
                     const auto tp0 = std::chrono::steady_clock::now();
+                    DGH_RANGE_PUSH("pack unit");
                     struct PackTimer {
                         Front* f; std::chrono::steady_clock::time_point t0;
-                        ~PackTimer() { const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); std::lock_guard<std::mutex> lk(f->err_mu); f->st.pack_seconds += dt; }
+                        ~PackTimer() { DGH_RANGE_POP(); const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); std::lock_guard<std::mutex> lk(f->err_mu); f->st.pack_seconds += dt; }
                     } pack_timer{this, tp0};
                     try {
                         hb->pre.reset();
@@ -483,7 +496,9 @@ int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunSta
         inflight.pop_front();
         const int g = (int)(hb->seq % (uint64_t)G);
         dgc_results r{};
+        DGH_RANGE_PUSH("dgc_collect");
         const int c = dgc_collect(hs[(size_t)g], &r);
+        DGH_RANGE_POP();
         on_gpu[(size_t)g]--;
         if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s collected batch %llu\n", prog, since(t0), (unsigned long long)hb->seq);
         if (c) {
@@ -524,9 +539,11 @@ int dispatch_batches(const ProgramOpts& opts, BatchFeed& feed, FILE* out, RunSta
         // the batch struct is read during submit only; the arrays it points to stay alive in `inflight`
         if (opts.verbose) fprintf(stderr, "%s-b200: %.3f s submit batch %llu (%u targets, %.1f MB) to GPU %d\n", prog, since(t0), (unsigned long long)seq, hb->n_targets, hb->arena_bytes / 1e6, g);
         int c;
+        DGH_RANGE_PUSH("dgc_submit");
         if (hb->daz) { const dgc_daz_batch zb = hb->daz->view(); c = dgc_submit_daz(hs[(size_t)g], &zb); }
         else if (hb->pre) { const dgc_pre_batch pb = hb->pre->view(); c = dgc_submit_pre(hs[(size_t)g], &pb); }
         else { const dgc_batch b = hb->view(); c = dgc_submit(hs[(size_t)g], &b); }
+        DGH_RANGE_POP();
         if (c) { rc = c; err = std::string("dgc_submit: ") + dgc_last_error(hs[(size_t)g]); feed.recycle(std::move(hb)); continue; }
         on_gpu[(size_t)g]++;
         stats.batches++;
