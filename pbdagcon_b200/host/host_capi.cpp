@@ -61,11 +61,12 @@ void* dgh_pack_file(const char* path, int fmt, uint32_t min_cov, int threads, ui
 // The dazcon front over a DB + LAS pair: every target with its backbone and the alignments rebuilt from the trace
 // points, packed as the C ABI takes them (same handle type as dgh_pack_file; array 9 = tgt_bb_off).
 void* dgh_pack_daz(const char* db, const char* las, uint32_t min_cov, uint32_t max_hits, int sort_cov, int proper, int threads,
-                   uint32_t batch_targets, double* seconds) {
+                   uint32_t batch_targets, double* seconds, const int* targets, int n_targets) {
     Packed* p = new Packed();
     dgh::ProgramOpts o;
     o.seqFile = db; o.alnFile = las; o.minCov = min_cov; o.maxHits = max_hits; o.sortCov = sort_cov != 0; o.properOvls = proper != 0;
     o.threads = threads;
+    for (int i = 0; i < n_targets; i++) o.targets.insert(targets[i]);   // 1-based ids, as dazcon's positional arguments
     if (batch_targets) o.batchTargets = batch_targets;
     const int rc = dgh::pack_daz(o, false, sink, p, p->st, p->err);
     if (rc && p->err.empty()) p->err = "pack_daz failed";
