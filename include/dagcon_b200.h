@@ -209,6 +209,48 @@ int dgc_submit_pre(dgc_handle* h, const dgc_pre_batch* batch);
 int dgc_debug_pre_strings(dgc_handle* h, const dgc_pre_batch* batch, uint8_t* out_q, uint8_t* out_t, uint64_t out_cap,
                           uint64_t* out_off, uint32_t* out_len, uint32_t* out_start);
 
+/* ---- the `-a` aligner for callers that must not allocate --------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel and same
+ * band schedule (64, 128, ... 8192) as dgc_submit_pre / dgc_debug_pre_strings, so the strings are the same bytes, but
+ * nothing is allocated, on the device or through any library: every pointer of dgc_pre_dev is a DEVICE pointer the
+ * caller owns, and the kernel's scratch (move matrices, record lists, slab offsets) is one file-scope `__device__`
+ * array of DGC_NOALLOC_SCRATCH_BYTES (+ 64 KB of lists) inside the library, which every GPU that loads the library holds until exit.
+ * Limits: n_recs <= DGC_NOALLOC_MAX_RECS, and every record's move matrix, (qlen + 1) * (2 * min(band, max(qlen,
+ * tseglen) + 1) + 1) bytes at the band it needs, must fit the scratch on its own; beyond either the call returns
+ * DGC_E_INVALID with the reason in `err` and launches nothing more (a batch larger than the scratch runs in waves).
+ * The call works on `stream` (a cudaStream_t, NULL = the default stream) and returns after synchronising it: the
+ * band schedule reads the records' states back between passes (into a buffer on its stack).
+ * ALL CALLS SHARE THE ONE ARRAY (per GPU): calls that overlap on the same GPU -- two host threads, two streams --
+ * race on it and corrupt each other's move matrices; serialise them.  The array keeps the last call's bytes; nothing
+ * in it has to start at zero (every cell a traceback reads is written by the same launch), and out_state, which does,
+ * is cleared by the call. */
+#define DGC_NOALLOC_MAX_RECS 4096u
+#define DGC_NOALLOC_SCRATCH_BYTES (64u << 20)
+typedef struct dgc_pre_dev {
+    uint32_t n_recs;
+    uint32_t reserved;
+    /* inputs, device memory */
+    const uint32_t* rec_start;      /* [n_recs] as dgc_pre_batch.rec_start */
+    const uint32_t* rec_strand;     /* [n_recs] 0 = '+', 1 = '-' */
+    const uint32_t* rec_qlen;       /* [n_recs] */
+    const uint32_t* rec_tseglen;    /* [n_recs] */
+    const uint32_t* rec_tlen;       /* [n_recs] length of the record's whole target (dgc_pre_batch.tgt_tlen of its target) */
+    const uint64_t* rec_q_off;      /* [n_recs] into arena (ASCII) */
+    const uint64_t* rec_t_off;
+    const uint8_t* arena;
+    /* outputs, device memory */
+    uint8_t* out_arena;             /* gapped strings; record k owns qlen + tseglen bytes at out_q_off[k] and at out_t_off[k] */
+    const uint64_t* out_q_off;      /* [n_recs] chosen by the caller */
+    const uint64_t* out_t_off;
+    uint32_t* out_len;              /* [n_recs] gapped columns (0 = nothing aligns) */
+    uint32_t* out_start;            /* [n_recs] Alignment::start (1-based, target orientation; SimpleAligner.cpp:49-62) */
+    uint32_t* out_tbegin;           /* [n_recs] target bases cut in front of / kept up to, within the segment */
+    uint32_t* out_tend;
+    uint32_t* out_state;            /* [n_recs] 1 = aligned, 3 = nothing aligns */
+} dgc_pre_dev;
+int dgc_pre_align_noalloc(int device, const dgc_pre_dev* args, void* stream, char* err, uint64_t err_cap);
+
 /* Synchronous convenience: submit + collect. */
 int dgc_consensus(dgc_handle* h, const dgc_batch* batch, dgc_results* out);
 

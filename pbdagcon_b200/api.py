@@ -21,7 +21,8 @@ BATCH_PACKED4 = 1
 EXPORTS = ["dgc_abi_version", "dgc_device_count", "dgc_create", "dgc_destroy", "dgc_last_error", "dgc_host_alloc",
            "dgc_host_free", "dgc_submit", "dgc_collect", "dgc_consensus", "dgc_upload", "dgc_run", "dgc_dbatch_free",
            "dgc_get_timings", "dgc_debug_normalize", "dgc_debug_graph", "dgc_debug_free",
-           "dgc_daz_set_db", "dgc_submit_daz", "dgc_debug_daz_strings", "dgc_submit_pre", "dgc_debug_pre_strings"]
+           "dgc_daz_set_db", "dgc_submit_daz", "dgc_debug_daz_strings", "dgc_submit_pre", "dgc_debug_pre_strings",
+           "dgc_pre_align_noalloc"]
 
 
 class DagconError(RuntimeError):
@@ -45,6 +46,17 @@ class CPreBatch(C.Structure):
                 ("tgt_tlen", C.c_void_p), ("tgt_rec_begin", C.c_void_p), ("rec_start", C.c_void_p), ("rec_strand", C.c_void_p),
                 ("rec_qlen", C.c_void_p), ("rec_tseglen", C.c_void_p), ("rec_q_off", C.c_void_p), ("rec_t_off", C.c_void_p),
                 ("arena", C.c_void_p), ("arena_bytes", C.c_uint64)]
+
+
+class CPreDev(C.Structure):
+    """dgc_pre_dev: every pointer is a DEVICE pointer the caller owns (dgc_pre_align_noalloc allocates nothing)."""
+    _fields_ = [("n_recs", C.c_uint32), ("reserved", C.c_uint32)] + \
+               [(k, C.c_void_p) for k in ("rec_start", "rec_strand", "rec_qlen", "rec_tseglen", "rec_tlen", "rec_q_off", "rec_t_off", "arena",
+                                          "out_arena", "out_q_off", "out_t_off", "out_len", "out_start", "out_tbegin", "out_tend", "out_state")]
+
+
+NOALLOC_MAX_RECS = 4096
+NOALLOC_SCRATCH_BYTES = 64 << 20
 
 
 class PreBatch:
@@ -126,6 +138,7 @@ def load_library():
     lib.dgc_debug_free.argtypes = [C.c_void_p]
     lib.dgc_submit_pre.argtypes = [H, C.POINTER(CPreBatch)]
     lib.dgc_debug_pre_strings.argtypes = [H, C.POINTER(CPreBatch), C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.dgc_pre_align_noalloc.argtypes = [C.c_int, C.POINTER(CPreDev), C.c_void_p, C.c_char_p, C.c_uint64]
     _lib = lib
     return lib
 

@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdarg>
 #include <condition_variable>
 #include <deque>
 #include <cstdio>
@@ -1425,6 +1426,55 @@ void worker_main(Slot* sp) {
 
 }  // namespace
 
+// ============================================================================ dgc_pre_align_noalloc: static scratch
+// The one scratch array of the allocation-free entry point (include/dagcon_b200.h): 64 KB of record lists for
+// k_pre_align (launch ids, slab offsets) followed by the move matrices.  Part of the module image: every GPU that
+// loads the library holds it until exit.  In HOST code the name below is only a stand-in for the symbol -- never a
+// device address: the address comes from cudaGetSymbolAddress, once per device (na_scratch()).
+namespace {
+
+constexpr size_t NA_LIST_BYTES = 64 * 1024;      // u32 ids[MAX_RECS] at 0, u64 tb_off[MAX_RECS] at 16 KB
+constexpr size_t NA_TBOFF_AT = 4 * (size_t)DGC_NOALLOC_MAX_RECS;
+static_assert(NA_TBOFF_AT + 8 * (size_t)DGC_NOALLOC_MAX_RECS <= NA_LIST_BYTES, "record lists fit their 64 KB");
+static __device__ __align__(256) unsigned char g_na_scratch[NA_LIST_BYTES + (size_t)DGC_NOALLOC_SCRATCH_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_na_mu;
+unsigned char* g_na_ptr[NA_MAX_DEVICES] = {};
+
+// the device address of g_na_scratch on `device`, which must be the current device
+cudaError_t na_scratch(int device, unsigned char** out) {
+    std::lock_guard<std::mutex> lk(g_na_mu);
+    if (!g_na_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_na_scratch);
+        if (e != cudaSuccess) return e;
+        g_na_ptr[device] = (unsigned char*)p;
+    }
+    *out = g_na_ptr[device];
+    return cudaSuccess;
+}
+
+// records no band can take (the existing path's tail of build_pre_batch): zero columns, start = tstart + 1
+__global__ void k_na_hopeless(const u32* ids, u32 n, const u32* rec_start, u32* out_len, u32* out_start, u32* tbeg, u32* tend, u32* state) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 r = ids[i];
+    out_len[r] = 0; out_start[r] = rec_start[r] + 1; tbeg[r] = 0; tend[r] = 0; state[r] = 3;
+}
+
+int na_fail(char* err, uint64_t cap, int rc, const char* fmt, ...) {
+    if (err && cap) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, (size_t)cap, fmt, ap);
+        va_end(ap);
+    }
+    return rc;
+}
+
+}  // namespace
+
 // ============================================================================ C ABI
 extern "C" {
 
@@ -1879,5 +1929,116 @@ int dgc_debug_graph(dgc_handle* h, dgc_dbatch* db, uint32_t target, int stage, c
 }
 
 void dgc_debug_free(char* text) { free(text); }
+
+// The `-a` aligner without a single allocation (header: no counterpart in the reference).
+// The band schedule and the wave planning are build_pre_batch's, on stack buffers; the kernel is
+// k_pre_align itself, its scratch the static array above.  No cudaMalloc / cudaFree / std::vector here.
+int dgc_pre_align_noalloc(int device, const dgc_pre_dev* a, void* stream, char* err, uint64_t err_cap) {
+    if (err && err_cap) err[0] = 0;
+    if (!a) return na_fail(err, err_cap, DGC_E_INVALID, "null arguments");
+    const uint32_t R = a->n_recs;
+    if (R > DGC_NOALLOC_MAX_RECS)
+        return na_fail(err, err_cap, DGC_E_INVALID, "n_recs %u is beyond DGC_NOALLOC_MAX_RECS (%u): split the batch", R, DGC_NOALLOC_MAX_RECS);
+    if (R == 0) return DGC_OK;
+    if (!a->rec_start || !a->rec_strand || !a->rec_qlen || !a->rec_tseglen || !a->rec_tlen || !a->rec_q_off || !a->rec_t_off || !a->arena ||
+        !a->out_arena || !a->out_q_off || !a->out_t_off || !a->out_len || !a->out_start || !a->out_tbegin || !a->out_tend || !a->out_state)
+        return na_fail(err, err_cap, DGC_E_INVALID, "null device pointer in dgc_pre_dev");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return na_fail(err, err_cap, DGC_E_NODEVICE, "no CUDA device (there is no CPU path)");
+    if (device < 0 || device >= ndev || device >= NA_MAX_DEVICES) return na_fail(err, err_cap, DGC_E_INVALID, "device %d out of range", device);
+    int prev_dev = device;
+    cudaGetDevice(&prev_dev);
+    cudaError_t e = cudaSetDevice(device);
+    unsigned char* scratch = nullptr;
+    if (e == cudaSuccess) e = na_scratch(device, &scratch);   // cudaGetSymbolAddress, once per device, with it current
+    if (e != cudaSuccess) {
+        if (prev_dev != device) cudaSetDevice(prev_dev);
+        return na_fail(err, err_cap, DGC_E_CUDA, "static scratch: %s", cudaGetErrorString(e));
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    u32* d_ids = (u32*)scratch;
+    u64* d_tboff = (u64*)(scratch + NA_TBOFF_AT);
+    u8* d_tb = scratch + NA_LIST_BYTES;
+    const uint64_t tb_budget = DGC_NOALLOC_SCRATCH_BYTES;
+
+    uint32_t h_qlen[DGC_NOALLOC_MAX_RECS], h_tlen[DGC_NOALLOC_MAX_RECS], h_state[DGC_NOALLOC_MAX_RECS];
+    uint32_t pending[DGC_NOALLOC_MAX_RECS], h_ids[DGC_NOALLOC_MAX_RECS];
+    uint64_t h_tboff[DGC_NOALLOC_MAX_RECS];
+    int rc = DGC_OK;
+#define NA_CU(call)                                                                                              \
+    do {                                                                                                         \
+        if (rc == DGC_OK && (e = (call)) != cudaSuccess) rc = na_fail(err, err_cap, DGC_E_CUDA, "%s: %s", #call, cudaGetErrorString(e)); \
+    } while (0)
+    NA_CU(cudaMemcpyAsync(h_qlen, a->rec_qlen, 4ull * R, cudaMemcpyDeviceToHost, st));
+    NA_CU(cudaMemcpyAsync(h_tlen, a->rec_tseglen, 4ull * R, cudaMemcpyDeviceToHost, st));
+    NA_CU(cudaMemsetAsync(a->out_state, 0, 4ull * R, st));
+    NA_CU(cudaStreamSynchronize(st));
+
+    PreArgs pa;
+    pa.rec_start = a->rec_start; pa.rec_tlen = a->rec_tlen; pa.aln_start = a->out_start;
+    pa.arena_in = a->arena; pa.q_off = (const u64*)a->rec_q_off; pa.t_off = (const u64*)a->rec_t_off; pa.q_len = a->rec_qlen; pa.t_len = a->rec_tseglen;
+    pa.strand = a->rec_strand; pa.tb = d_tb; pa.tb_off = d_tboff; pa.rec_ids = d_ids;
+    pa.arena_out = a->out_arena; pa.out_q_off = (const u64*)a->out_q_off; pa.out_t_off = (const u64*)a->out_t_off; pa.out_len = a->out_len;
+    pa.t_begin = a->out_tbegin; pa.t_end = a->out_tend; pa.state = a->out_state;
+
+    uint32_t n_pending = R;
+    for (uint32_t k = 0; k < R; k++) pending[k] = k;
+    for (uint32_t band = 64; rc == DGC_OK && n_pending && band <= PA_MAX_BAND; band *= 2) {
+        const uint32_t warps = band <= 512 ? 4u : 1u;
+        const size_t smem = (size_t)warps * 2 * (2 * band + 1 + 2 * PA_G) * sizeof(int);
+        if (smem > 48 * 1024) NA_CU(cudaFuncSetAttribute(k_pre_align, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        uint32_t done = 0;
+        while (rc == DGC_OK && done < n_pending) {   // waves that fit the static move-matrix area
+            uint64_t tb = 0;
+            uint32_t n = 0;
+            while (done + n < n_pending) {
+                const uint32_t k = pending[done + n];
+                const uint64_t full = (uint64_t)std::max(h_qlen[k], h_tlen[k]) + 1;
+                const uint64_t W = 2 * std::min<uint64_t>(band, full) + 1;
+                const uint64_t need = (((uint64_t)h_qlen[k] + 1) * W + 15) & ~15ull;
+                if (need > tb_budget) {
+                    rc = na_fail(err, err_cap, DGC_E_INVALID,
+                                 "record %u (%u x %u bases) needs a move matrix of %llu bytes at band %u: beyond the static scratch "
+                                 "(DGC_NOALLOC_SCRATCH_BYTES = %u); use dgc_submit_pre for it",
+                                 k, h_qlen[k], h_tlen[k], (unsigned long long)need, band, (unsigned)DGC_NOALLOC_SCRATCH_BYTES);
+                    break;
+                }
+                if (tb + need > tb_budget) break;
+                h_tboff[n] = tb; h_ids[n] = k;
+                tb += need;
+                n++;
+            }
+            if (rc != DGC_OK) break;
+            NA_CU(cudaMemcpyAsync(d_tboff, h_tboff, 8ull * n, cudaMemcpyHostToDevice, st));
+            NA_CU(cudaMemcpyAsync(d_ids, h_ids, 4ull * n, cudaMemcpyHostToDevice, st));
+            if (rc == DGC_OK) {
+                pa.n_launch = n; pa.band = band; pa.warps = warps;
+                k_pre_align<<<(n + warps - 1) / warps, warps * 32, smem, st>>>(pa);
+                NA_CU(cudaGetLastError());
+            }
+            NA_CU(cudaStreamSynchronize(st));   // the lists and the move matrices are reused by the next wave
+            done += n;
+        }
+        NA_CU(cudaMemcpyAsync(h_state, a->out_state, 4ull * R, cudaMemcpyDeviceToHost, st));
+        NA_CU(cudaStreamSynchronize(st));
+        if (rc != DGC_OK) break;
+        uint32_t m = 0;
+        for (uint32_t i = 0; i < n_pending; i++)
+            if (h_state[pending[i]] == 2) pending[m++] = pending[i];
+        n_pending = m;
+    }
+    if (rc == DGC_OK && n_pending) {   // beyond the widest band: zero-column alignments
+        NA_CU(cudaMemcpyAsync(d_ids, pending, 4ull * n_pending, cudaMemcpyHostToDevice, st));
+        if (rc == DGC_OK) {
+            k_na_hopeless<<<(n_pending + 127) / 128, 128, 0, st>>>(d_ids, n_pending, a->rec_start, a->out_len, a->out_start, a->out_tbegin, a->out_tend,
+                                                                  a->out_state);
+            NA_CU(cudaGetLastError());
+        }
+        NA_CU(cudaStreamSynchronize(st));
+    }
+#undef NA_CU
+    if (prev_dev != device) cudaSetDevice(prev_dev);
+    return rc;
+}
 
 }  // extern "C"
