@@ -374,7 +374,7 @@ int launch_build(Slot& s, dgc_dbatch& db, uint32_t first, uint32_t count, uint32
     ba.tgt_status = s.t_status.as<u32>(); ba.rec_off = s.rec_off.as<u64>(); ba.tgt_V = s.t_V.as<u32>();
     ba.pool_cap = s.pool_cap.as<u32>(); ba.acc_off = s.pos_off.as<u64>();
     ba.norm = s.norm.as<u16>(); ba.a_off = s.o_off.as<u64>(); ba.a_len = s.o_len.as<u32>();
-    ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>();
+    ba.a_start = s.o_start.as<u32>(); ba.a_flags = s.o_flags.as<u32>(); ba.a_tkept = s.o_tkept.as<u32>();
     ba.rec = s.rec.as<u8>();
     ba.tgt_status_out = s.t_status.as<u32>(); ba.tgt_nv = s.t_nv.as<u32>(); ba.tgt_pool_top = s.t_pool_top.as<u32>();
     // List lengths per position are bytes unless a target of the launch has so many alignments that a backbone vertex

@@ -32,7 +32,7 @@ struct __align__(16) Hdr {
     u32 out_ptr;  // 8-byte word index (from the arena base) of out-slot 0
     u32 in_ptr;   // 8-byte word index of in-slot 0
     int weight;
-    int cov;      // coverage of _bbMap[v] (bestPath, :407); an insertion vertex holds its bbmap here until the build folds
+    int cov;      // coverage of _bbMap[v] (bestPath, :407)
     union {
         float score;
         int cnt;
@@ -218,6 +218,7 @@ struct Build2Args {
     const u32* a_len;
     const u32* a_start;
     const u32* a_flags;
+    const u32* a_tkept;   // backbone positions each alignment consumes (normalise kernels): coverage is known before the replay
     u8* rec;
     u32* tgt_status_out;
     u32* tgt_nv;
@@ -321,8 +322,13 @@ __device__ __forceinline__ void b2_edge(const B2Ctx<DT>& c, u32 prev, u32 cur) {
         const u32 n = prev == 0 ? *c.s_enter_out : c.acc.dout[prev];
         const u32 ptr = prev == 0 ? c.enter_out : (n <= BB_OUT_CAP ? gv_inline_out(ph) : b2_hdr(c, ph)->out_ptr);
         OSlot* o = (OSlot*)(c.base + (size_t)ptr * 8);
-        for (u32 i = 0; i < n; i++)
-            if (o[i].dst == ch) { o[i].cv++; return; }
+#pragma unroll 1
+        for (u32 i = 0; i < n; i += 4) {   // first match in list order; four independent loads per round trip
+            const u32 i1 = min(i + 1, n - 1), i2 = min(i + 2, n - 1), i3 = min(i + 3, n - 1);
+            const u32 d0 = o[i].dst, d1 = o[i1].dst, d2 = o[i2].dst, d3 = o[i3].dst;
+            const u32 j = d0 == ch ? i : d1 == ch ? i1 : d2 == ch ? i2 : d3 == ch ? i3 : NIL;
+            if (j != NIL) { o[j].cv++; return; }
+        }
         b2_append_out(c, prev, ch);
         b2_append_in(c, cur, ph);
         return;
@@ -372,7 +378,8 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
 
     // ctor: AlnGraphBoost(size_t) :41-62 / AlnGraphBoost(const std::string&) :16-39
     for (u32 p = tid; p < nbb; p += BT) {
-        c.acc.cov[p] = 0; c.acc.w[p] = 0; c.acc.c[p] = 0; c.acc.b[p] = 0;
+        ((int*)c.acc.cov)[p] = 0;   // cov and w (adjacent u16 arrays) start as one int per position: the coverage differences below
+        c.acc.c[p] = 0; c.acc.b[p] = 0;
         c.acc.dout[p] = p <= L ? 1 : 0;
         c.acc.din[p] = p >= 1 ? 1 : 0;
         u8* r = c.base + (size_t)REC_UNIT * 2 * p;
@@ -403,6 +410,39 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
     }
     __syncthreads();
     if (s_status != T_OK) { if (tid == 0) a.tgt_status_out[t] = s_status; return; }
+
+    // Coverage of every backbone position, before the replay: an alignment covers [start, start + tkept) -- every one of
+    // its match and deletion columns consumes the next position (:75-92) -- so the counts are a prefix sum of +1 / -1
+    // marks.  An insertion vertex can then be written ONCE with the coverage of the backbone vertex it maps to
+    // (bestPath reads _g[_bbMap[v]].coverage, :407); the pass that patched every insertion record after the replay
+    // (a second DRAM round trip per record) is gone.
+    {
+        int* dcov = (int*)c.acc.cov;
+        for (u32 k = a0 + tid; k < a1; k += BT) {
+            if (a.a_flags[k] & AF_SKIP) continue;
+            const u32 tk = a.a_tkept[k], st = a.a_start[k];
+            if (tk) { atomicAdd(&dcov[st], 1); atomicAdd(&dcov[st + tk], -1); }   // st + tk <= L + 1 (k_target_plan)
+        }
+        __syncthreads();
+        const u32 per = (nbb + BT - 1) / BT, lo = min(nbb, tid * per), hi = min(nbb, lo + per);
+        u32 sum = 0;
+        for (u32 p = lo; p < hi; p++) sum += (u32)dcov[p];
+        u32 ex_s, ex_m, tot_s, tot_m;
+        block_scan2(sum, 0, ex_s, ex_m, tot_s, tot_m, sa, sb);
+        u32 run = ex_s;
+        for (u32 p = lo; p < hi; p++) { run += (u32)dcov[p]; dcov[p] = (int)run; }
+        __syncthreads();
+        // int per position -> the u16 cov array in place, BT positions per round: a round writes bytes that only rounds
+        // up to itself have read
+        for (u32 r0 = 0; r0 < nbb; r0 += BT) {
+            const u32 p = r0 + tid;
+            const int v = p < nbb ? dcov[p] : 0;
+            __syncthreads();
+            if (p < nbb) c.acc.cov[p] = (u16)v;
+        }
+        for (u32 p = tid; p < nbb; p += BT) c.acc.w[p] = 0;   // every read of the ints is behind the last barrier
+        __syncthreads();
+    }
 
     u32 ins_base = nbb;  // id of the next insertion vertex
     for (u32 k = a0; k < a1; k++) {
@@ -451,14 +491,14 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
             for (int j = 0; j < CPT; j++) {
                 const u32 p = bbpos[j];
                 if (kind[j] == 1 || kind[j] == 2) {
-                    c.acc.cov[p]++;                 // _g[_bbMap[curr]].coverage++
+                    // _g[_bbMap[curr]].coverage++ is in acc.cov already (counted before the replay)
                     c.acc.b[p] = (u8)tc[j];         // .base = targetBase (the last alignment in order wins)
                     if (kind[j] == 1) c.acc.w[p]++;
                 } else if (kind[j] == 3) {
                     const u32 hh = cur[j] + nbb;
                     Hdr h;
                     h.bfv = q[j]; h.deg = 0x10001u; h.out_ptr = gv_inline_out(hh); h.in_ptr = gv_inline_in(hh);
-                    h.weight = 1; h.cov = (int)p; h.cnt = 0; h.best = NIL;
+                    h.weight = 1; h.cov = p < nbb ? (int)c.acc.cov[p] : 0; h.cnt = 0; h.best = NIL;   // coverage of _bbMap[v]
                     *b2_hdr(c, hh) = h;
                 }
                 if (kind[j] == 1 || kind[j] == 3) {
@@ -478,8 +518,7 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
         if (n == 0) __syncthreads();
     }
     __syncthreads();
-    // fold the running sums into the backbone headers, then give every insertion vertex the coverage of the
-    // backbone vertex it maps to (bestPath reads _g[_bbMap[v]].coverage, :407)
+    // fold the running sums into the backbone headers
     const u8* bbstr = a.tgt_bb_off ? a.arena + a.tgt_bb_off[t] : nullptr;
     for (u32 p = tid; p < nbb; p += BT) {
         Hdr* hp = b2_hdr(c, 2 * p);
@@ -497,11 +536,6 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
         if (p <= L) ((OSlot*)(c.base + (size_t)h.out_ptr * 8))[0].cv = c.acc.c[p];
     }
     const u32 nv = ins_base;
-    for (u32 v = nbb + tid; v < nv; v += BT) {
-        Hdr* hv = b2_hdr(c, v + nbb);
-        const u32 bm = (u32)hv->cov;
-        hv->cov = bm < nbb ? (int)c.acc.cov[bm] : 0;
-    }
     if (tid == 0) {
         a.tgt_nv[t] = nv;
         a.tgt_pool_top[t] = s_pool_top;
