@@ -64,7 +64,11 @@ struct GV {           // one target's graph
 // headers after that.  Each of those was a separate DRAM miss (ncu r01b: 45 % of the stall samples on three loads).
 // So whenever a lane first touches a vertex it asks L2 for the whole record and, once the record's first slots have
 // arrived, for the records those slots name: the chain then runs one step behind its own prefetches.
+#ifdef GV_PF_L1   // experiment: ask for the line in L1 as well
+__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+#else
 __device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#endif
 __device__ __forceinline__ void gv_prefetch_rec(const GV& g, u32 h) {
     if (h < g.nunits) {  // a slot past a list's length holds stale bytes: never form an address outside the arena
         const u8* r = g.base + (size_t)h * REC_UNIT;
