@@ -742,6 +742,125 @@ __device__ __forceinline__ void m2_queue_append(const GV& g, u32 ready, bool min
     tail = __shfl_sync(FULLMASK, v, 31u - (u32)__clz((int)ready));
 }
 
+// mergeInNodes(u) (:162-215) by the whole warp, for the shape almost every merge has: every member of a group is a plain
+// chain vertex (one in-edge, one out-edge -- the edge to u), the members' predecessors n1 are distinct and none of them
+// has an edge to the survivor yet.  Lane j holds in-slot j of u (`s`, header words `d`, taken before any merge: the
+// std::map snapshot of :167-181); `dup` = the lane's vertex is in a group of two or more.  Groups go in ascending
+// (signed) base order, members in list order.  Per member ni != an, all members at once:
+//   :186-191  the count of ni's out-edge and ni's weight go to an
+//   :196-208  n1 -> an does not exist: add_edge(n1, an) with the count / visited flag of n1 -> ni, i.e. n1's out-list gets
+//             (an) at its end and an's in-list gets n1, in member order
+//   :209      markForReaper(ni): ni leaves n1's out-list and u's in-list, order of the rest kept
+//   :212      mergeInNodes(an): an's predecessors are the members' n1; only if two of them qualify does the scalar code run
+// Anything else (a member with more edges, shared or already-connected predecessors, lists that would outgrow their
+// place) goes to the scalar m2_merge_in, which takes its own snapshot of what is left.  Returns the target's status.
+__device__ __noinline__ u32 m2_merge_in_warp(T2Ctx& c, const u32 u, const u32 nin, const u32 s, const uint2 d, const bool dup) {
+    GV& g = c.g;
+    const u32 lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    const bool have = lane < nin;
+    const u32 skey = (u32)((int)(signed char)(d.x & 0xFFu) + 128);
+    u32 removed = 0, vis_removed = 0;
+    bool pending = dup, fallback = false;
+    for (;;) {
+        const u32 k = __reduce_min_sync(FULLMASK, pending ? skey : 0xFFFFFFFFu);
+        if (k == 0xFFFFFFFFu) break;
+        const bool in_grp = pending && skey == k;
+        const u32 M = __ballot_sync(FULLMASK, in_grp);
+        const u32 la = (u32)__ffs((int)M) - 1;              // the survivor `an` = first member in list order
+        const u32 an = __shfl_sync(FULLMASK, s, la);
+        u32 n1 = NIL, cvo = 0, wgt = 0, e_ni = NIL, d1 = 0, cvn = 0, bfv_m = 0;
+        uint2 dn1 = make_uint2(0u, 0u);
+        OSlot* o1 = nullptr;
+        bool ok = true;
+        if (in_grp) {
+            const bool is_a = lane == la;
+            const Hdr m = *gv_hdr(g, s);
+            bfv_m = m.bfv;
+            ok = m.deg == 0x10001u;
+            if (ok) {
+                wgt = (u32)m.weight;
+                const OSlot so = *gv_out(g, m.out_ptr);
+                cvo = so.cv;
+                ok = so.dst == u;
+                n1 = *gv_in(g, m.in_ptr);
+                if (is_a) ok = ok && m.in_ptr == gv_inline_in(s) && (u32)__popc(M) <= REC_IN_CAP;   // an's in-list grows in place
+                const Hdr* h1 = gv_hdr(g, n1);
+                dn1 = *(const uint2*)h1;
+                d1 = dn1.y >> 16;
+                o1 = gv_out(g, h1->out_ptr);
+                ok = ok && d1 <= 32;
+                if (ok) {
+#pragma unroll 1
+                    for (u32 i = 0; i < d1; i++) {
+                        const u32 dst = o1[i].dst;
+                        if (dst == s && e_ni == NIL) e_ni = i;
+                        if (dst == an && !is_a) ok = false;      // edge(n1, an) exists (:201): scalar
+                    }
+                    if (e_ni == NIL) ok = false; else cvn = o1[e_ni].cv;
+                }
+            }
+            if (__popc(__match_any_sync(M, n1)) != 1) ok = false;   // two members behind one predecessor: scalar
+        }
+        if (__any_sync(FULLMASK, in_grp && !ok)) { fallback = true; break; }
+        if (in_grp) {
+            const bool is_a = lane == la;
+            const u32 cnt_sum = __reduce_add_sync(M, is_a ? 0u : (cvo & ~VISBIT));
+            const u32 w_sum = __reduce_add_sync(M, is_a ? 0u : wgt);
+            const u32 nvis = (u32)__popc(__ballot_sync(M, !is_a && (cvn & VISBIT)));
+            const u32 gone_vis = __ballot_sync(M, !is_a && (cvo & VISBIT));
+            const u32 others = M & ~(1u << la);
+            Hdr* han = gv_hdr(g, an);
+            if (is_a) {
+                gv_out(g, han->out_ptr)->cv = cvo + cnt_sum;
+                han->weight = (int)(wgt + w_sum);
+                han->deg = (u32)__popc(M) | 0x10000u;
+                han->bfv = bfv_m + (nvis << 16);
+            } else {
+#pragma unroll 1
+                for (u32 i = e_ni; i + 1 < d1; i++) o1[i] = o1[i + 1];
+                OSlot ns;
+                ns.dst = an; ns.cv = cvn;
+                o1[d1 - 1] = ns;
+                gv_in(g, gv_inline_in(an))[1 + __popc(others & lt)] = n1;
+                *(uint2*)gv_hdr(g, s) = make_uint2((bfv_m & 0xFFFFu) | (NF_DELETED << 8), 0u);
+            }
+            removed |= others;
+            vis_removed |= gone_vis;
+        }
+        removed = __shfl_sync(FULLMASK, removed, la);
+        vis_removed = __shfl_sync(FULLMASK, vis_removed, la);
+        __syncwarp();
+        // mergeInNodes(an) :212 -- an's in-list is the members' n1 in lane order; their out-degrees did not change
+        bool rec = false;
+        if (in_grp) {
+            const bool c1 = (dn1.y >> 16) == 1;
+            const u32 g1 = __match_any_sync(M, c1 ? (dn1.x & 0xFFu) : 0x100u + lane);
+            rec = c1 && __popc(g1) > 1;
+        }
+        if (__any_sync(FULLMASK, rec)) {
+            if (lane == 0) m2_merge_in(c, an);
+            __syncwarp();
+            if (__shfl_sync(FULLMASK, g.status, 0) != T_OK) break;
+        }
+        pending = pending && !in_grp;
+    }
+    // u's in-list without the merged members, order kept; their (visited) edges no longer count at u
+    if (removed) {
+        Hdr* pu = gv_hdr(g, u);
+        const u32 surv = __ballot_sync(FULLMASK, have) & ~removed;
+        const u32 in_ptr = pu->in_ptr, deg = pu->deg, bfv = pu->bfv;
+        __syncwarp();
+        if (have && !((removed >> lane) & 1u)) gv_in(g, in_ptr)[__popc(surv & lt)] = s;
+        if (lane == 0) { pu->deg = (deg & 0xFFFF0000u) | (u32)__popc(surv); pu->bfv = bfv - ((u32)__popc(vis_removed) << 16); }
+    }
+    __syncwarp();
+    if (fallback) {
+        if (lane == 0) m2_merge_in(c, u);
+        __syncwarp();
+    }
+    return __shfl_sync(FULLMASK, g.status, 0);
+}
+
 __device__ __forceinline__ bool warp2_setup(const Serial2Args& a, u32& t, T2Ctx& c) {
     const u32 idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (idx >= a.count) return false;
@@ -785,21 +904,23 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
         // ---- mergeInNodes(u): is there a group of >= 2 predecessors with out_degree 1 and the same base?
         u32 nin = hu.deg & 0xFFFFu;
         if (nin >= 2) {
-            bool need = nin > 32;  // only exit gets that wide: let the scalar code decide
-            if (!need) {
+            if (nin > 32) {  // only exit gets that wide: the scalar code decides and merges
+                if (lane == 0) m2_merge_in(c, u);
+                __syncwarp();
+                status = __shfl_sync(FULLMASK, g.status, 0);
+                hu = *pu;
+            } else {
                 const bool have = lane < nin;
                 const u32 s = have ? gv_in(g, hu.in_ptr)[lane] : 0u;
                 uint2 d = make_uint2(0u, 0u);
                 if (have) d = *(const uint2*)gv_hdr(g, s);
                 const bool cand = have && (d.y >> 16) == 1;
                 const u32 grp = __match_any_sync(FULLMASK, cand ? (d.x & 0xFFu) : 0x100u + lane);
-                need = cand && __popc(grp) > 1;
-            }
-            if (__any_sync(FULLMASK, need)) {
-                if (lane == 0) m2_merge_in(c, u);
-                __syncwarp();
-                status = __shfl_sync(FULLMASK, g.status, 0);
-                hu = *pu;
+                const bool dup = cand && __popc(grp) > 1;
+                if (__any_sync(FULLMASK, dup)) {
+                    status = m2_merge_in_warp(c, u, nin, s, d, dup);
+                    hu = *pu;
+                }
             }
         }
         // ---- mergeOutNodes(u), then mark the out-edges visited and enqueue the successors that became ready
