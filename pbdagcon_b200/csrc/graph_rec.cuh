@@ -946,7 +946,8 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
             }
             if (ready) tail = s0.dst;
             __syncwarp();
-            head = pu->best;
+            // u's queue link was in its header when it was popped (NIL = u was the tail: what follows is what this step appended)
+            head = hu.best != NIL ? hu.best : (ready ? s0.dst : NIL);
             continue;
         }
         if (nout > 32) {  // enter (one edge per alignment start): scalar
@@ -1049,6 +1050,7 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
                                 ((OSlot*)(ra + REC_OUT_OFF))[1 + __popc(newl & ((1u << lane) - 1u))] = ns;
                             }
                             if (leader) { const Hdr* hx = gv_hdr(g, x); xdeg = hx->deg; xinp = hx->in_ptr; }   // every leader's header at once
+                            }
                             // markForReaper(member) :260
                             if (!is_a) *(uint2*)gv_hdr(g, sl.dst) = make_uint2((d.x & 0xFFFFu) | (NF_DELETED << 8), 0u);
                         }
@@ -1123,11 +1125,13 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
             if (ready && (bfv & (NF_QUEUED << 8))) status = T_INTERNAL;
             if (ready) bfv |= NF_QUEUED << 8;
             if (have && bfv != d.x) gv_hdr(g, sl.dst)->bfv = bfv;
-            m2_queue_append(g, __ballot_sync(FULLMASK, ready), ready, sl.dst, tail, lane);
+            const u32 rdy = __ballot_sync(FULLMASK, ready);
+            m2_queue_append(g, rdy, ready, sl.dst, tail, lane);
             if (__any_sync(FULLMASK, status != T_OK)) status = T_INTERNAL;
+            const u32 first = __shfl_sync(FULLMASK, sl.dst, rdy ? (u32)__ffs((int)rdy) - 1 : 0u);
+            head = hu.best != NIL ? hu.best : (rdy ? first : NIL);
         }
         __syncwarp();
-        head = pu->best;
     }
     if (lane == 0) {
         a.tgt_pool_top[t] = g.pool_top;
@@ -1198,6 +1202,7 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
             if (cs > best_score) { best_score = cs; best_dst = cd; }  // strict >: an earlier chunk's maximum stays
         }
         // ---- count this vertex off at its predecessors; those with all successors scored join the queue
+        u32 first_app = NIL;  // first vertex this step appends: the next pop when n was the queue's tail
         if (nin == 1) {  // a chain link again: one predecessor, handled warp-uniformly without the append machinery
             const u32 s = gv_in(g, hn.in_ptr)[0];
             Hdr* hs = gv_hdr(g, s);
@@ -1209,7 +1214,7 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
                 hs->cnt = (int)k;
                 if (ready) { hs->best = NIL; gv_hdr(g, tail)->best = s; }
             }
-            if (ready) tail = s;
+            if (ready) { tail = s; first_app = s; }
         } else
         for (u32 b0 = 0; b0 < nin; b0 += 32) {
             const bool have = b0 + lane < nin;
@@ -1233,10 +1238,11 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
 #endif
             }
             __syncwarp();
-            m2_queue_append(g, __ballot_sync(FULLMASK, ready), ready, s, tail, lane);
+            const u32 rdy = __ballot_sync(FULLMASK, ready);
+            m2_queue_append(g, rdy, ready, s, tail, lane);
+            if (rdy && first_app == NIL) first_app = __shfl_sync(FULLMASK, s, (u32)__ffs((int)rdy) - 1);
         }
-        __syncwarp();
-        const u32 nx = pn->best;
+        const u32 nx = hn.best != NIL ? hn.best : first_app;  // the queue link was in n's header when it was popped
         __syncwarp();
         if (lane == 0) {
             pn->score = best_dst != NIL ? best_score : 0.0f;  // an absent map key reads as 0.0f (:401)
@@ -1259,6 +1265,9 @@ __device__ __forceinline__ void best_sweep(const Serial2Args& a, const u32 t, co
     u32 nfrag = 0, steps = 0, prev = ENTER, status = T_OK;
     for (;;) {
         const Hdr hp = *gv_hdr(g, prev);
+        // the path is a chain of dependent loads, but it mostly runs along the backbone, whose records sit at known places:
+        // ask for the backbone vertex a few positions ahead (records this far from exit left L2 long ago)
+        if (prev < 2 * (L + 1) && g.nunits) pf_l2(g.base + (size_t)min(prev + 16u, 2 * (L + 1)) * REC_UNIT);
         const u32 b = hp.bfv & 0xFFu;
         const int w = hp.weight;
         if (b != eb && b != xb) {
