@@ -64,10 +64,12 @@ struct GV {           // one target's graph
 // headers after that.  Each of those was a separate DRAM miss (ncu r01b: 45 % of the stall samples on three loads).
 // So whenever a lane first touches a vertex it asks L2 for the whole record and, once the record's first slots have
 // arrived, for the records those slots name: the chain then runs one step behind its own prefetches.
-#ifdef GV_PF_L1   // experiment: ask for the line in L1 as well
-__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
-#else
+// Into L1 as well: the warp that asks is the only reader of its target's records (measured: 256 targets 74.7 -> 69.7 ms,
+// 10 000 targets unchanged against prefetch.global.L2; -DGV_PF_L2_ONLY restores that form).
+#ifdef GV_PF_L2_ONLY
 __device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#else
+__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 #endif
 __device__ __forceinline__ void gv_prefetch_rec(const GV& g, u32 h) {
     if (h < g.nunits) {  // a slot past a list's length holds stale bytes: never form an address outside the arena
@@ -1049,7 +1051,16 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
                                 ns.dst = x; ns.cv = Cx;
                                 ((OSlot*)(ra + REC_OUT_OFF))[1 + __popc(newl & ((1u << lane) - 1u))] = ns;
                             }
-                            if (leader) { const Hdr* hx = gv_hdr(g, x); xdeg = hx->deg; xinp = hx->in_ptr; }   // every leader's header at once
+                            if (leader) {   // every leader's header at once
+                                const Hdr* hx = gv_hdr(g, x);
+                                xdeg = hx->deg; xinp = hx->in_ptr;
+                                const u32 nmx = (u32)__popc(Mx);
+                                if (is_a && nmx == 1) leader = false;       // only `an` itself points there: the in-list stays as it is
+                                else if ((xdeg & 0xFFFFu) == nmx) {          // every in-edge of x comes from this group (no parallel
+                                    *gv_in(g, xinp) = an;                    // edges): what is left of the list is [an]
+                                    gv_hdr(g, x)->deg = (xdeg & 0xFFFF0000u) | 1u;
+                                    leader = false;
+                                }
                             }
                             // markForReaper(member) :260
                             if (!is_a) *(uint2*)gv_hdr(g, sl.dst) = make_uint2((d.x & 0xFFFFu) | (NF_DELETED << 8), 0u);
