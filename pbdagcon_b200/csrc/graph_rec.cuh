@@ -990,6 +990,18 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
             if (g.nunits) pf_l2(rv + 32);
             if (d.y >> 16) gv_prefetch_rec(g, o01.x);
             if ((d.y >> 16) > 1) gv_prefetch_rec(g, o01.z);
+#ifdef GV_PF_WIDE
+            // a successor with more out-edges (a backbone vertex with insertions behind it): when IT is popped every lane
+            // waits for the slowest of those headers, so ask for the next four as well (same line as the first two slots)
+            if ((d.y >> 16) > 2 && g.nunits) {
+                const uint4 o23 = *(const uint4*)(rv + REC_OUT_OFF + 16), o45 = *(const uint4*)(rv + REC_OUT_OFF + 32);
+                const u32 nd = d.y >> 16;
+                if (o23.x < g.nunits) pf_l2(g.base + (size_t)o23.x * REC_UNIT);
+                if (nd > 3 && o23.z < g.nunits) pf_l2(g.base + (size_t)o23.z * REC_UNIT);
+                if (nd > 4 && o45.x < g.nunits) pf_l2(g.base + (size_t)o45.x * REC_UNIT);
+                if (nd > 5 && o45.z < g.nunits) pf_l2(g.base + (size_t)o45.z * REC_UNIT);
+            }
+#endif
 #endif
         }
         {

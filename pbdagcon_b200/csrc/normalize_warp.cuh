@@ -44,6 +44,15 @@ struct NwSmem {
 __device__ __forceinline__ u32 nw_byte(const u32* w, int j) { return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu; }
 __device__ __forceinline__ u32 nw_undot(u32 b) { return b == DOT ? DASH : b; }
 
+// how many of the word's bytes [first, first + 4) below `nvalid` are bases, i.e. neither '-' nor '.' (four at a time:
+// a byte of x is zero where the character is '-', of y where it is '.'; bit 7 of ((v & 0x7F) + 0x7F) | v says "non-zero")
+__device__ __forceinline__ u32 nw_count_bases(u32 w, u32 nvalid, u32 first) {
+    const u32 x = w ^ 0x2D2D2D2Du, y = w ^ 0x2E2E2E2Eu;
+    u32 nz = ((((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & (((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y)) & 0x80808080u;
+    if (nvalid < first + 4u) nz &= nvalid > first ? (1u << (8u * (nvalid - first))) - 1u : 0u;
+    return (u32)__popc(nz);
+}
+
 // One expanded column of the transducer, branch-free (the lanes of a warp see different columns; every data
 // dependent branch here would serialise them).  ct/cq: bases consumed so far, ot/oq: bases located before this
 // column (tile-relative).  Returns the output column, or 0 when it is gap/gap.
@@ -193,12 +202,10 @@ __global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp
         // ---- base counts, ranks, compacted streams
         u32 nT = 0, nQ = 0;
 #pragma unroll
-        for (int j = 0; j < 32; j++)
-            if ((u32)j < nvalid) { nT += nw_undot(nw_byte(tw, j)) != DASH; nQ += nw_undot(nw_byte(qw, j)) != DASH; }
+        for (int k = 0; k < 8; k++) { nT += nw_count_bases(tw[k], nvalid, 4 * k); nQ += nw_count_bases(qw[k], nvalid, 4 * k); }
         u32 mT = 0, mQ = 0;
 #pragma unroll
-        for (int j = 0; j < 8; j++)
-            if ((u32)j < mvalid) { mT += nw_undot(nw_byte(tm, j)) != DASH; mQ += nw_undot(nw_byte(qm, j)) != DASH; }
+        for (int k = 0; k < 2; k++) { mT += nw_count_bases(tm[k], mvalid, 4 * k); mQ += nw_count_bases(qm[k], mvalid, 4 * k); }
         const u32 inc = warp_incl_scan(nT | (nQ << 16), lane);
         const u32 tot = __shfl_sync(0xFFFFFFFFu, inc, 31);
         const u32 ex = inc - (nT | (nQ << 16));
@@ -248,9 +255,10 @@ __global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp
         const u32 oinc = warp_incl_scan(nout, lane);
         __syncwarp();
 #pragma unroll 1
-        for (u32 l = 0; l < 32; l++) {  // row l of the staging area, by the whole warp
+        for (u32 l4 = 0; l4 < 32; l4 += 4) {  // four rows of the staging area at a time, eight lanes each: a row holds 32-40
+            const u32 l = l4 + (lane >> 3);     // columns, and consecutive rows are consecutive in the output
             const u32 nl = __shfl_sync(0xFFFFFFFFu, nout, l), dl = __shfl_sync(0xFFFFFFFFu, oinc - nout, l);
-            for (u32 i = lane; i < nl; i += 32) out[m + dl + i] = sm.stage[l * NW_STG + i];
+            for (u32 i = lane & 7u; i < nl; i += 8) out[m + dl + i] = sm.stage[l * NW_STG + i];
         }
         m += __shfl_sync(0xFFFFFFFFu, oinc, 31);
         carry = __shfl_sync(0xFFFFFFFFu, lead_out, 31);
