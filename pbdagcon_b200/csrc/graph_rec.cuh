@@ -990,18 +990,6 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
             if (g.nunits) pf_l2(rv + 32);
             if (d.y >> 16) gv_prefetch_rec(g, o01.x);
             if ((d.y >> 16) > 1) gv_prefetch_rec(g, o01.z);
-#ifdef GV_PF_WIDE
-            // a successor with more out-edges (a backbone vertex with insertions behind it): when IT is popped every lane
-            // waits for the slowest of those headers, so ask for the next four as well (same line as the first two slots)
-            if ((d.y >> 16) > 2 && g.nunits) {
-                const uint4 o23 = *(const uint4*)(rv + REC_OUT_OFF + 16), o45 = *(const uint4*)(rv + REC_OUT_OFF + 32);
-                const u32 nd = d.y >> 16;
-                if (o23.x < g.nunits) pf_l2(g.base + (size_t)o23.x * REC_UNIT);
-                if (nd > 3 && o23.z < g.nunits) pf_l2(g.base + (size_t)o23.z * REC_UNIT);
-                if (nd > 4 && o45.x < g.nunits) pf_l2(g.base + (size_t)o45.x * REC_UNIT);
-                if (nd > 5 && o45.z < g.nunits) pf_l2(g.base + (size_t)o45.z * REC_UNIT);
-            }
-#endif
 #endif
         }
         {
@@ -1012,7 +1000,7 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
             if (__any_sync(FULLMASK, dup)) {
                 const u32 skey = (u32)((int)(signed char)key + 128);  // std::map<char,...> iterates signed chars ascending
                 // ---- can the whole merge run warp-parallel?  Yes when every member is a plain chain vertex (one
-                // in-edge, one unvisited out-edge, inline lists), no member is the target of another member, and a
+                // in-edge, one unvisited out-edge, inline lists) and a
                 // group has at most 6 members (the survivor's inline out-slots then hold every distinct target).
                 u32 x = NIL, cvx = 0, wgt = 0;
                 bool ok = true;
@@ -1024,12 +1012,8 @@ __device__ __forceinline__ u32 merge_sweep(const Serial2Args& a, const u32 t, T2
                     x = s0.dst; cvx = s0.cv;
                     ok = d.y == 0x10001u && optr == gv_inline_out(sl.dst) && !(cvx & VISBIT) && __popc(grp) <= 6;
                 }
-                bool clash = false;
-                for (u32 m = __ballot_sync(FULLMASK, dup); m; m &= m - 1) {
-                    const u32 xj = __shfl_sync(FULLMASK, x, __ffs((int)m) - 1);
-                    clash |= dup && sl.dst == xj;
-                }
-                if (!__any_sync(FULLMASK, (dup && !ok) || clash)) {
+                // (no member can be the target of another member: its only in-edge, d.y == 0x10001, is the one from u)
+                if (!__any_sync(FULLMASK, dup && !ok)) {
                     u32 removed = 0;
                     bool pending = dup;
                     for (;;) {
