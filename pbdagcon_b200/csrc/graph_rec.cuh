@@ -261,22 +261,22 @@ struct B2Ctx {
 template <typename DT>
 __device__ __forceinline__ Hdr* b2_hdr(const B2Ctx<DT>& c, u32 h) { return (Hdr*)(c.base + (size_t)h * REC_UNIT); }
 
-// append (p -> dst handle, count 1) to backbone vertex p's out-list
+// append (p -> dst handle, count 1) to backbone vertex p's out-list; returns the slot it went to (NIL: it did not)
 template <typename DT>
-__device__ __forceinline__ void b2_append_out(const B2Ctx<DT>& c, u32 p, u32 dsth) {
+__device__ __forceinline__ u32 b2_append_out(const B2Ctx<DT>& c, u32 p, u32 dsth) {
     u32 n, ptr;
     if (p == 0) {
         n = (*c.s_enter_out)++;
         ptr = c.enter_out;
     } else {
         n = c.acc.dout[p];
-        if (n >= acc_max_deg<DT>()) { *c.s_status = T_TOO_MANY; return; }
+        if (n >= acc_max_deg<DT>()) { *c.s_status = T_TOO_MANY; return NIL; }
         c.acc.dout[p] = (DT)(n + 1);
         ptr = n <= BB_OUT_CAP ? gv_inline_out(2 * p) : b2_hdr(c, 2 * p)->out_ptr;
         const u32 have = n <= BB_OUT_CAP ? BB_OUT_CAP : (u32)((const u64*)c.base)[ptr - 1];
         if (n == have) {  // full: the list moves into a pool block twice the size (a backbone vertex has at most A+1 out-edges)
             const u32 cap = min(2u * have, max(c.A + 2, have + 1)), blk = atomicAdd(c.s_pool_top, cap + 1);
-            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.dout[p] = (DT)n; return; }
+            if (blk + cap + 1 > c.pool_end) { *c.s_status = T_POOL; c.acc.dout[p] = (DT)n; return NIL; }
             ((u64*)c.base)[blk] = cap;
             const OSlot* o = (const OSlot*)(c.base + (size_t)ptr * 8);
             OSlot* no = (OSlot*)(c.base + (size_t)(blk + 1) * 8);
@@ -288,6 +288,7 @@ __device__ __forceinline__ void b2_append_out(const B2Ctx<DT>& c, u32 p, u32 dst
     OSlot s;
     s.dst = dsth; s.cv = 1;
     ((OSlot*)(c.base + (size_t)ptr * 8))[n] = s;
+    return n;
 }
 template <typename DT>
 __device__ __forceinline__ void b2_append_in(const B2Ctx<DT>& c, u32 p, u32 srch) {
@@ -324,7 +325,25 @@ __device__ __forceinline__ void b2_edge(const B2Ctx<DT>& c, u32 prev, u32 cur) {
     const u32 ph = gv_handle(prev, nbb), ch = gv_handle(cur, nbb);
     if (prev_bb && cur_bb) {
         if (cur == prev + 1) { c.acc.c[prev]++; return; }  // the ctor edge p -> p+1
-        // a backbone->backbone skip (deletion run, alignment start or end): it may exist already
+        // a backbone->backbone skip (deletion run, alignment start or end): it may exist already.  Searching prev's
+        // out-list means reading a record that left the caches many alignments ago, with the whole block waiting at the
+        // tile's barrier.  With byte-wide list lengths (<= 252 alignments) the ctor-edge count above stays below 256, and
+        // its upper byte remembers prev's FIRST skip edge: (positions skipped) << 5 | slot, 0 = none yet, 0xFF = there is
+        // one that does not fit this code.  A deletion of the same length at the same place -- the usual case -- is then
+        // one fire-and-forget add to a known slot; prev has one successor per alignment, so the byte has one writer.
+        if (sizeof(DT) == 1 && prev != 0) {
+            const u32 cw = c.acc.c[prev], hi = cw >> 8, k1 = cur - prev - 1;
+            if (hi == 0) {   // no skip edge yet: the list holds the ctor edge and edges to insertion vertices only
+                const u32 slot = b2_append_out(c, prev, ch);
+                b2_append_in(c, cur, ph);
+                c.acc.c[prev] = (u16)(cw | ((k1 <= 6 && slot <= 31) ? ((k1 << 5) | slot) << 8 : 0xFF00u));
+                return;
+            }
+            if (hi != 0xFFu && (hi >> 5) == k1 && c.acc.dout[prev] <= BB_OUT_CAP) {   // still in the record itself
+                atomicAdd(&((OSlot*)(c.base + (size_t)gv_inline_out(ph) * 8))[hi & 31u].cv, 1u);
+                return;
+            }
+        }
         const u32 n = prev == 0 ? *c.s_enter_out : c.acc.dout[prev];
         const u32 ptr = prev == 0 ? c.enter_out : (n <= BB_OUT_CAP ? gv_inline_out(ph) : b2_hdr(c, ph)->out_ptr);
         OSlot* o = (OSlot*)(c.base + (size_t)ptr * 8);
@@ -539,7 +558,7 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
         h.weight = (inner ? 1 : 0) + (int)c.acc.w[p];
         h.cov = (int)cv;
         *hp = h;
-        if (p <= L) ((OSlot*)(c.base + (size_t)h.out_ptr * 8))[0].cv = c.acc.c[p];
+        if (p <= L) ((OSlot*)(c.base + (size_t)h.out_ptr * 8))[0].cv = sizeof(DT) == 1 ? (c.acc.c[p] & 0xFFu) : c.acc.c[p];   // upper byte: b2_edge's skip-edge note
     }
     const u32 nv = ins_base;
     if (tid == 0) {
