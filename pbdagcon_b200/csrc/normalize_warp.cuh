@@ -42,13 +42,19 @@ struct NwSmem {
 };
 
 __device__ __forceinline__ u32 nw_byte(const u32* w, int j) { return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu; }
-__device__ __forceinline__ u32 nw_undot(u32 b) { return b == DOT ? DASH : b; }
+// '.' -> '-' in all four bytes of a staged word (Alignment.cpp:133-146 does it to both strings before anything else): a byte
+// of y is zero where the character is '.', z has 0x80 there, and '.' ^ '-' == 3
+__device__ __forceinline__ u32 nw_undot4(u32 w) {
+    const u32 y = w ^ 0x2E2E2E2Eu;
+    const u32 z = ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
+    return w ^ ((z >> 7) | (z >> 6));
+}
 
-// how many of the word's bytes [first, first + 4) below `nvalid` are bases, i.e. neither '-' nor '.' (four at a time:
-// a byte of x is zero where the character is '-', of y where it is '.'; bit 7 of ((v & 0x7F) + 0x7F) | v says "non-zero")
+// how many of the word's bytes [first, first + 4) below `nvalid` are bases, i.e. not '-' (four at a time: a byte of x is
+// zero where the character is '-'; bit 7 of ((v & 0x7F) + 0x7F) | v says "non-zero")
 __device__ __forceinline__ u32 nw_count_bases(u32 w, u32 nvalid, u32 first) {
-    const u32 x = w ^ 0x2D2D2D2Du, y = w ^ 0x2E2E2E2Eu;
-    u32 nz = ((((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & (((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y)) & 0x80808080u;
+    const u32 x = w ^ 0x2D2D2D2Du;   // (the word is undotted already)
+    u32 nz = (((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
     if (nvalid < first + 4u) nz &= nvalid > first ? (1u << (8u * (nvalid - first))) - 1u : 0u;
     return (u32)__popc(nz);
 }
@@ -99,7 +105,7 @@ __device__ __forceinline__ u32 nw_chunk(u32 (&qw)[8], u32 (&tw)[8], u32 nvalid, 
             const u32 j = w * 4 + b;
             const bool valid = j < nvalid;
             // columns past the chunk behave as gap/gap: no state change, no output
-            const u32 qb = valid ? nw_undot((qword >> (8 * b)) & 0xFFu) : DASH, tb = valid ? nw_undot((tword >> (8 * b)) & 0xFFu) : DASH;
+            const u32 qb = valid ? (qword >> (8 * b)) & 0xFFu : DASH, tb = valid ? (tword >> (8 * b)) & 0xFFu : DASH;   // the words were undotted when they were loaded
             const bool mism = (qb != tb) & (qb != DASH) & (tb != DASH);
             const bool lastcol = has_last & (j + 1 == nvalid);
             // a mismatch is a deletion column followed by an insertion column (Alignment.cpp:147-159)
@@ -194,6 +200,10 @@ __global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp
             tw[0] = y0.x; tw[1] = y0.y; tw[2] = y0.z; tw[3] = y0.w; tw[4] = y1.x; tw[5] = y1.y; tw[6] = y1.z; tw[7] = y1.w;
             const uint2 xm = ((const uint2*)sm.q)[NW_TR / 8 + lane], ym = ((const uint2*)sm.t)[NW_TR / 8 + lane];
             qm[0] = xm.x; qm[1] = xm.y; tm[0] = ym.x; tm[1] = ym.y;
+#pragma unroll
+            for (int k = 0; k < 8; k++) { qw[k] = nw_undot4(qw[k]); tw[k] = nw_undot4(tw[k]); }
+#pragma unroll
+            for (int k = 0; k < 2; k++) { qm[k] = nw_undot4(qm[k]); tm[k] = nw_undot4(tm[k]); }
         }
         const u32 col0 = lane * 32;                       // first tile column of this lane (window-relative)
         const u32 nvalid = col0 < min(nwin, NW_TR) ? min(32u, min(nwin, NW_TR) - col0) : 0u;
@@ -218,7 +228,7 @@ __global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp
 #pragma unroll
             for (int j = 0; j < 32; j++)
                 if ((u32)j < nvalid) {
-                    const u32 tb = nw_undot(nw_byte(tw, j)), qb = nw_undot(nw_byte(qw, j));
+                    const u32 tb = nw_byte(tw, j), qb = nw_byte(qw, j);
                     if (tb != DASH) sm.ts[rt++] = (u8)tb;
                     if (qb != DASH) sm.qs[rq++] = (u8)qb;
                 }
@@ -226,7 +236,7 @@ __global__ void __launch_bounds__(NW_WARPS * 32, NW_MIN_BLOCKS) k_normalize_warp
 #pragma unroll
             for (int j = 0; j < 8; j++)
                 if ((u32)j < mvalid) {
-                    const u32 tb = nw_undot(nw_byte(tm, j)), qb = nw_undot(nw_byte(qm, j));
+                    const u32 tb = nw_byte(tm, j), qb = nw_byte(qm, j);
                     if (tb != DASH) sm.ts[rt++] = (u8)tb;
                     if (qb != DASH) sm.qs[rq++] = (u8)qb;
                 }
