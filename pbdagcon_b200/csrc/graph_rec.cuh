@@ -331,6 +331,17 @@ __device__ __forceinline__ void b2_edge(const B2Ctx<DT>& c, u32 prev, u32 cur) {
         // its upper byte remembers prev's FIRST skip edge: (positions skipped) << 5 | slot, 0 = none yet, 0xFF = there is
         // one that does not fit this code.  A deletion of the same length at the same place -- the usual case -- is then
         // one fire-and-forget add to a known slot; prev has one successor per alignment, so the byte has one writer.
+        if (sizeof(DT) == 1 && prev == 0) {
+            // enter -> the vertex an alignment starts on: enter's out-list is as long as the target has alignments and sits in
+            // the pool.  The upper byte of the START vertex's match weight (<= 252 as well; the thread that counts the first
+            // column's match is the one that adds this edge) remembers the edge's slot + 1.
+            const u32 ww = c.acc.w[cur], hi = ww >> 8;
+            if (hi) { atomicAdd(&((OSlot*)(c.base + (size_t)c.enter_out * 8))[hi - 1].cv, 1u); return; }
+            const u32 slot = b2_append_out(c, 0u, ch);
+            b2_append_in(c, cur, ph);
+            if (slot < 255u) { c.acc.w[cur] = (u16)(ww | ((slot + 1) << 8)); return; }
+            return;   // (cannot happen: at most 252 alignments)
+        }
         if (sizeof(DT) == 1 && prev != 0) {
             const u32 cw = c.acc.c[prev], hi = cw >> 8, k1 = cur - prev - 1;
             if (hi == 0) {   // no skip edge yet: the list holds the ctor edge and edges to insertion vertices only
@@ -476,15 +487,30 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
         const u16* cols = a.norm + a.a_off[k];
         // block-uniform replay state, kept in registers by every thread: no serial section, no barrier to publish it
         u32 carry_t = 0, carry_i = 0, last = ENTER;
+#ifdef B2_COLS_AHEAD   // experiment: the columns of a tile are loaded one tile ahead
+        u32 ahead = 0;
+#pragma unroll
+        for (int j = 0; j < CPT; j++) ahead |= (tid * CPT + j < n ? (u32)cols[tid * CPT + j] : 0u) << (16 * j);
+#endif
         for (u32 c0 = 0; c0 < n; c0 += TILE) {
             const u32 cb = c0 + tid * CPT;
             u32 q[CPT], tc[CPT], kind[CPT];  // kind: 0 none, 1 match, 2 deletion, 3 insertion
             u32 nadv = 0, nins = 0, lastp = 0;
+#ifdef B2_COLS_AHEAD
+            const u32 now = ahead;
+            ahead = 0;
+#pragma unroll
+            for (int j = 0; j < CPT; j++) ahead |= (cb + TILE + j < n ? (u32)cols[cb + TILE + j] : 0u) << (16 * j);
+#endif
 #pragma unroll
             for (int j = 0; j < CPT; j++) {
                 kind[j] = 0; q[j] = 0; tc[j] = 0;
                 if (cb + j < n) {
+#ifdef B2_COLS_AHEAD
+                    const u32 col = (now >> (16 * j)) & 0xFFFFu;
+#else
                     const u32 col = cols[cb + j];
+#endif
                     q[j] = col & 0xFFu; tc[j] = col >> 8;
                     // column classes exactly as addAln tests them (:75, :84, :93)
                     if (q[j] == tc[j]) kind[j] = 1;
@@ -555,7 +581,7 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
         h.bfv = b | (NF_BACKBONE << 8);
         const u32 dout = p == ENTER ? s_enter_out : c.acc.dout[p], din = p == EXIT ? s_exit_in : c.acc.din[p];
         h.deg = din | (dout << 16);
-        h.weight = (inner ? 1 : 0) + (int)c.acc.w[p];
+        h.weight = (inner ? 1 : 0) + (int)(sizeof(DT) == 1 ? (c.acc.w[p] & 0xFFu) : c.acc.w[p]);   // upper byte: b2_edge's enter-edge note
         h.cov = (int)cv;
         *hp = h;
         if (p <= L) ((OSlot*)(c.base + (size_t)h.out_ptr * 8))[0].cv = sizeof(DT) == 1 ? (c.acc.c[p] & 0xFFu) : c.acc.c[p];   // upper byte: b2_edge's skip-edge note
