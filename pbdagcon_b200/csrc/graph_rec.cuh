@@ -487,30 +487,15 @@ __global__ void __launch_bounds__(BT, BUILD_MIN_BLOCKS) k_build_graph2(Build2Arg
         const u16* cols = a.norm + a.a_off[k];
         // block-uniform replay state, kept in registers by every thread: no serial section, no barrier to publish it
         u32 carry_t = 0, carry_i = 0, last = ENTER;
-#ifdef B2_COLS_AHEAD   // experiment: the columns of a tile are loaded one tile ahead
-        u32 ahead = 0;
-#pragma unroll
-        for (int j = 0; j < CPT; j++) ahead |= (tid * CPT + j < n ? (u32)cols[tid * CPT + j] : 0u) << (16 * j);
-#endif
         for (u32 c0 = 0; c0 < n; c0 += TILE) {
             const u32 cb = c0 + tid * CPT;
             u32 q[CPT], tc[CPT], kind[CPT];  // kind: 0 none, 1 match, 2 deletion, 3 insertion
             u32 nadv = 0, nins = 0, lastp = 0;
-#ifdef B2_COLS_AHEAD
-            const u32 now = ahead;
-            ahead = 0;
-#pragma unroll
-            for (int j = 0; j < CPT; j++) ahead |= (cb + TILE + j < n ? (u32)cols[cb + TILE + j] : 0u) << (16 * j);
-#endif
 #pragma unroll
             for (int j = 0; j < CPT; j++) {
                 kind[j] = 0; q[j] = 0; tc[j] = 0;
                 if (cb + j < n) {
-#ifdef B2_COLS_AHEAD
-                    const u32 col = (now >> (16 * j)) & 0xFFFFu;
-#else
                     const u32 col = cols[cb + j];
-#endif
                     q[j] = col & 0xFFu; tc[j] = col >> 8;
                     // column classes exactly as addAln tests them (:75, :84, :93)
                     if (q[j] == tc[j]) kind[j] = 1;
