@@ -372,6 +372,62 @@ def test_config2_shape_invariants_at_scale(api, synth):
         assert r1.frags(t) == o.consensus(L, alns, mode=MODE_PIPELINE, trim=50, min_weight=8, min_len=500)["frags"], f"target {t}"
 
 
+def test_skip_edge_and_enter_edge_notes(api, synth):
+    """The build remembers a position's first skip edge (deletion length <= 6, slot <= 31) and the slot of the enter edge
+    that starts at a vertex in spare accumulator bytes (graph_rec.cuh b2_edge).  Everything around those codes: deletions of
+    lengths 1..9 leaving the same vertex in every order (the remembered one, others, lengths that do not fit the code),
+    the same deletion after the vertex's out-list has outgrown its record (30 insertions first), alignments that start on
+    the same vertex many times, start with a deletion, or consist of deletions only."""
+    o = checker()
+    rng = random.Random(4242)
+    L = 60
+    bb = bytes(rng.choice(b"ACGT") for _ in range(L))
+
+    def aln(start, ops):
+        """ops over target positions from `start` (1-based): 'm' match, ('d', k) delete k bases, ('i', base) insert."""
+        q, t, p = b"", b"", start - 1
+        for op in ops:
+            if op == "m":
+                q += bb[p:p + 1]; t += bb[p:p + 1]; p += 1
+            elif op[0] == "d":
+                q += b"-" * op[1]; t += bb[p:p + op[1]]; p += op[1]
+            else:
+                q += bytes([op[1]]); t += b"-"
+        return (q, t, start)
+
+    alns = []
+    other = lambda p: rng.choice([c for c in b"ACGT" if c != bb[p]])
+    # deletions of every length after vertex 10 (target positions 11..), in shuffled order, several times each
+    lens = [1, 2, 3, 6, 7, 9, 1, 2, 7, 6, 3, 1, 9, 2, 1]
+    rng.shuffle(lens)
+    for k in lens:
+        alns.append(aln(6, ["m"] * 5 + [("d", k)] + ["m"] * 8))
+    # vertex 30: thirty insertions first (its out-list leaves the record), then the same two deletions again and again
+    for _ in range(30):
+        alns.append(aln(26, ["m"] * 5 + [("i", other(30))] + ["m"] * 6))
+    for k in [2, 2, 5, 2, 5, 8, 2]:
+        alns.append(aln(26, ["m"] * 5 + [("d", k)] + ["m"] * 6))
+    # starts: the same start vertex many times, a start that is a deletion, deletions only, a start on vertex 1
+    for _ in range(9):
+        alns.append(aln(40, ["m"] * 10))
+    alns.append(aln(40, [("d", 3)] + ["m"] * 6))
+    alns.append(aln(41, [("d", 4)]))
+    alns.append(aln(1, ["m"] * 12))
+    alns.append(aln(1, ["m"] * 3 + [("d", 2)] + ["m"] * 4))
+    rng.shuffle(alns)
+    eng = api.Consensus(min_cov=1, min_len=1, trim=0, flags=api.F_NO_NORMALIZE)
+    b = _batch(api, synth, [(L, None, alns)])
+    exp = o.consensus(L, alns, mode=MODE_DUMP_PRE | MODE_DUMP_POST | MODE_MERGE, trim=0, min_weight=1, min_len=1)
+    lines = exp["dump"].split("\n")
+    nl = (len(lines) - 1) // 2
+    pre, post = "\n".join(lines[:nl]) + "\n", "\n".join(lines[nl:2 * nl]) + "\n"
+    assert eng.debug_graph(b, 0, 0) == pre
+    assert eng.debug_graph(b, 0, 1) == post
+    res = eng(b)
+    eng.close()
+    assert res.status[0] == api.T_OK and res.frags(0) == exp["frags"]
+
+
 @pytest.mark.parametrize("A", [251, 252, 253, 254, 300])
 def test_backbone_vertex_degree_edges(api, synth, A):
     """A backbone vertex whose out-list (and its successor's in-list) grows to A + 1 entries: every alignment matches
